@@ -1,0 +1,225 @@
+"""Training driver: the reference's ``dist_train`` (ref.py:56-236) as a reusable ``Trainer``.
+
+Flow: discover rank -> build/shard the data -> replicate the model from rank 0
+-> per epoch: banner, one step per batch (local forward/MSE/backward, gradient sync fused with
+the SGD-momentum update), print the local loss of the last batch.
+
+Two compute backends:
+
+* ``cuda``  - the product.  Hand-written sm_100a kernels from ``libb200dp.so`` (``ops/``): fused
+              SIMT kernel for tiny nets, tcgen05/TMA GEMMs + fused MSE for real widths, fused
+              peer-memory all-reduce + SGD.  Selected automatically when a GPU is present; it
+              raises if the native library is missing (no silent fallback on a GPU box).
+* ``torch`` - plain PyTorch ops (``ops/reference.py``) for boxes without a GPU (CPU plumbing
+              config, parity tests, the gloo multi-process tests).
+"""
+from __future__ import annotations
+
+import math
+import time
+from typing import Any, Dict, List, Optional
+
+import torch
+
+from . import checkpoint as ckpt
+from .config import TrainConfig
+from .data import BatchPlan, Shard, load_shard, load_validation
+from .models.mlp import FlatMLP, MLPSpec
+from .ops import reference as ref_ops
+from .parallel.comm import Comm, SingleComm
+from .parallel.grad_sync import make_host_sync
+from .utils.logging import JsonlLogger, emit, epoch_banner, loss_line
+from .utils.timing import PhaseTimer
+
+
+class TorchCompute:
+    """Local forward + loss + backward with PyTorch ops (CPU path / oracle)."""
+    name = "torch"
+
+    def __init__(self, flat: FlatMLP, cfg: TrainConfig):
+        self.flat = flat
+
+    def prepare_batch(self, x: torch.Tensor, y: torch.Tensor):
+        return x, y
+
+    def loss_and_grads(self, x, y) -> torch.Tensor:
+        return ref_ops.mlp_loss_and_grads(self.flat, x, y)
+
+    def predict(self, x) -> torch.Tensor:
+        return ref_ops.mlp_forward(self.flat, x).to(torch.float32)
+
+
+def resolve_backend(cfg: TrainConfig, device: torch.device) -> str:
+    if cfg.backend != "auto":
+        if cfg.backend == "cuda" and device.type != "cuda":
+            raise RuntimeError("backend=cuda needs a GPU")
+        return cfg.backend
+    return "cuda" if device.type == "cuda" else "torch"
+
+
+class Trainer:
+    def __init__(self, cfg: TrainConfig, comm: Optional[Comm] = None,
+                 device: Optional[torch.device] = None, shard: Optional[Shard] = None):
+        self.cfg = cfg.validate()
+        self.comm = comm if comm is not None else SingleComm()
+        self.device = torch.device(device) if device is not None else torch.device("cpu")
+        self.backend = resolve_backend(cfg, self.device)
+        self.rank, self.world = self.comm.rank, self.comm.size
+        self.log = JsonlLogger(cfg.log_jsonl if self.rank == 0 else None)
+        self.timer = PhaseTimer(self.device, enabled=bool(cfg.log_jsonl))
+        self.history: List[Dict[str, Any]] = []
+        self.start_epoch = 0
+
+        # ---- data (ref.py:66-146) ----
+        self.shard = shard if shard is not None else load_shard(cfg, self.comm)
+        self.counts = list(self.shard.counts)
+        self.val = load_validation(cfg) if (cfg.val_frac > 0 and self.rank == 0) else None
+
+        # ---- model replicas (ref.py:83-88) + sync strategy ----
+        self.spec = MLPSpec(cfg.layer_sizes())
+        if self.backend == "cuda":
+            from .ops.cuda_backend import build_cuda_runtime   # raises if libb200dp.so is missing
+            rt = build_cuda_runtime(self)
+            self.flat, self.compute, self.sync = rt.flat, rt.compute, rt.sync
+            self._runtime = rt
+        else:
+            self.flat = FlatMLP(self.spec, self.device, cfg.dtype)
+            self.compute = TorchCompute(self.flat, cfg)
+            self.sync = make_host_sync(cfg.sync, self.comm, self.counts, cfg.grad_weighting)
+            self._runtime = None
+        self._replicate_initial_state()
+        if cfg.resume:
+            self.load_checkpoint(cfg.resume)
+
+        batch = cfg.batch_size if cfg.use_batch_size else None
+        self.plan = BatchPlan(self.shard.rows, batch, cfg.shuffle, seed=cfg.seed + 1 + self.rank)
+        self.x, self.y = self.compute.prepare_batch(self.shard.x.to(self.device),
+                                                    self.shard.y.to(self.device))
+
+    # ------------------------------------------------------------------ init
+    def _replicate_initial_state(self):
+        """Root initialises with ``manual_seed(seed)`` and everybody adopts root's parameters
+        (ref.py:66-69, 84-88)."""
+        cfg = self.cfg
+        if cfg.init == "device" and self.device.type == "cuda":
+            # same seed on every rank -> identical replicas without moving any bytes
+            self.flat.init_on_device(cfg.seed)
+            return
+        if self.rank == 0:
+            self.flat.init_like_reference(cfg.seed)
+        if self.world > 1:
+            if self._runtime is not None and self._runtime.device_broadcast is not None:
+                self._runtime.device_broadcast(self.flat.params)
+                self.flat.sync_shadow()
+            else:
+                sd = self.comm.bcast(self.flat.state_dict() if self.rank == 0 else None, root=0)
+                self.flat.load_state_dict(sd)
+
+    # ------------------------------------------------------------------ step
+    def step(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
+        """One synchronous data-parallel step (ref.py:164-211).  Returns the local pre-update loss
+        as a 0-dim device tensor (no host sync)."""
+        with self.timer.phase("fwd_bwd"):
+            loss = self.compute.loss_and_grads(x, y)
+        with self.timer.phase("sync_update"):
+            self.sync.sync_and_step(self.flat, self.cfg.lr, self.cfg.momentum)
+        return loss
+
+    def train(self) -> List[Dict[str, Any]]:
+        cfg = self.cfg
+        for epoch in range(self.start_epoch, cfg.nepochs):
+            emit(epoch_banner(epoch), cfg.quiet)                                # ref.py:152
+            t0 = time.perf_counter()
+            loss = None
+            for idx in self.plan.epoch():                                       # ref.py:155
+                xb, yb = (self.x, self.y) if idx is None else \
+                    (self.x[idx.to(self.x.device)], self.y[idx.to(self.y.device)])
+                loss = self.step(xb, yb)
+            if loss is None:                                                    # rank owns no rows
+                self.flat.grads.zero_()
+                self.sync.sync_and_step(self.flat, cfg.lr, cfg.momentum)
+                loss_val = float("nan")
+            else:
+                loss_val = float(loss.item())                                   # ref.py:224
+            emit(loss_line(self.rank, loss_val), cfg.quiet)
+            rec = {"epoch": epoch, "rank": self.rank, "loss": loss_val,
+                   "epoch_s": time.perf_counter() - t0}
+            if cfg.global_loss or cfg.log_jsonl:
+                rec["global_loss"] = self._global_loss(loss_val)
+                if cfg.global_loss and self.rank == 0:
+                    emit(f"global loss (sample-weighted): {rec['global_loss']}", cfg.quiet)
+            if self.val is not None:
+                rec["val_loss"] = self.evaluate(*self.val)
+                emit(f"validation loss (rank 0): {rec['val_loss']}", cfg.quiet)
+            if cfg.check_replicas_every and (epoch + 1) % cfg.check_replicas_every == 0:
+                self.assert_replicas_identical()
+            if cfg.checkpoint and cfg.checkpoint_every and (epoch + 1) % cfg.checkpoint_every == 0:
+                self.save_checkpoint(cfg.checkpoint, epoch + 1)
+            self.history.append(rec)
+            if self.rank == 0 and cfg.log_jsonl:
+                self.log.log(**rec, phases_ms=self.timer.mean_ms(),
+                             samples_per_s=sum(self.counts) / max(rec["epoch_s"], 1e-12))
+        if cfg.checkpoint:
+            self.save_checkpoint(cfg.checkpoint, cfg.nepochs)
+        return self.history
+
+    # ------------------------------------------------------------------ extras
+    def _global_loss(self, local: float) -> float:
+        pairs = self.comm.allgather((local, self.shard.rows))
+        tot = sum(n for _, n in pairs)
+        return sum(l * n for l, n in pairs if n > 0 and not math.isnan(l)) / max(tot, 1)
+
+    @torch.no_grad()
+    def evaluate(self, x: torch.Tensor, y: torch.Tensor) -> float:
+        """MSE on held-out rows (the reference's dead validation/test stubs, ref.py:213-236)."""
+        pred = self.compute.predict(x.to(self.device))
+        return float(((pred - y.to(self.device)) ** 2).mean().item())
+
+    @torch.no_grad()
+    def predict(self, x: torch.Tensor) -> torch.Tensor:
+        return self.compute.predict(x.to(self.device))
+
+    def assert_replicas_identical(self) -> None:
+        """Debug-mode race detector: every rank must hold the same parameter bytes."""
+        prints = self.comm.allgather(self.flat.fingerprint())
+        if len(set(prints)) != 1:
+            raise RuntimeError(f"replicas diverged: parameter fingerprints {prints}")
+
+    def save_checkpoint(self, path: str, epoch: int) -> None:
+        if self._runtime is not None:
+            self._runtime.gather_optimizer_state()
+        if self.rank == 0:
+            ckpt.save_checkpoint(path, self.flat, epoch, self.cfg.asdict())
+        self.comm.barrier()
+
+    def load_checkpoint(self, path: str) -> None:
+        payload = ckpt.load_checkpoint(path, self.flat)
+        self.start_epoch = int(payload.get("epoch", 0))
+
+    def close(self):
+        self.log.close()
+        self.sync.close()
+        if self._runtime is not None:
+            self._runtime.close()
+
+
+def dist_train(args, comm: Optional[Comm] = None, device=None) -> Trainer:
+    """Schedule a distributed training job - the reference's entry point (ref.py:56).  ``args`` may
+    be the reference's own argparse Namespace (lr, momentum, batch_size, nepochs) or a
+    ``TrainConfig``."""
+    from .config import config_from_args
+    from .launch import bind_device, discover, init_process_group
+    from .parallel.comm import world_comm
+
+    cfg = args if isinstance(args, TrainConfig) else config_from_args(args)
+    if comm is None:
+        info = discover()
+        dev = bind_device(info) if device is None else torch.device(device)
+        if info.world_size > 1:
+            init_process_group(info)
+        comm = world_comm()
+    else:
+        dev = torch.device(device) if device is not None else torch.device("cpu")
+    trainer = Trainer(cfg, comm, dev)
+    trainer.train()
+    return trainer

@@ -1,0 +1,87 @@
+"""Launcher contract: rank / world discovery and device binding.
+
+The reference is started with ``mpiexec -n N python script.py`` (README:12) and reads its rank
+from ``MPI.COMM_WORLD`` (ref.py:61-63).  Here a process learns who it is from the environment, in
+this order: torchrun (``RANK/WORLD_SIZE/LOCAL_RANK``), Open MPI (``OMPI_COMM_WORLD_*``), MPICH /
+Intel MPI / Slurm PMI (``PMI_RANK/PMI_SIZE``, ``PMIX_RANK``, ``SLURM_PROCID``).  No variables means a
+single process.  One process drives one GPU (``cudaSetDevice(LOCAL_RANK)``).
+"""
+from __future__ import annotations
+
+import os
+from dataclasses import dataclass
+from typing import Mapping, Optional
+
+
+@dataclass(frozen=True)
+class RankInfo:
+    rank: int
+    world_size: int
+    local_rank: int
+    launcher: str
+    master_addr: str = "127.0.0.1"
+    master_port: int = 29500
+
+
+def _first_int(env: Mapping[str, str], *names: str) -> Optional[int]:
+    for n in names:
+        v = env.get(n)
+        if v not in (None, ""):
+            return int(v)
+    return None
+
+
+def discover(env: Optional[Mapping[str, str]] = None) -> RankInfo:
+    env = os.environ if env is None else env
+    addr = env.get("MASTER_ADDR", "127.0.0.1")
+    port = int(env.get("MASTER_PORT", "29500"))
+    if "RANK" in env and "WORLD_SIZE" in env:
+        rank, world = int(env["RANK"]), int(env["WORLD_SIZE"])
+        local = _first_int(env, "LOCAL_RANK")
+        return RankInfo(rank, world, rank if local is None else local, "torchrun", addr, port)
+    if "OMPI_COMM_WORLD_RANK" in env:
+        rank = int(env["OMPI_COMM_WORLD_RANK"])
+        world = int(env.get("OMPI_COMM_WORLD_SIZE", "1"))
+        local = _first_int(env, "OMPI_COMM_WORLD_LOCAL_RANK")
+        return RankInfo(rank, world, rank if local is None else local, "openmpi", addr, port)
+    rank = _first_int(env, "PMI_RANK", "PMIX_RANK", "SLURM_PROCID")
+    if rank is not None:
+        world = _first_int(env, "PMI_SIZE", "SLURM_NTASKS") or 1
+        local = _first_int(env, "MPI_LOCALRANKID", "SLURM_LOCALID")
+        return RankInfo(rank, world, rank if local is None else local, "pmi", addr, port)
+    return RankInfo(0, 1, 0, "single", addr, port)
+
+
+def bind_device(info: RankInfo):
+    """Returns the torch.device this rank drives (cuda:LOCAL_RANK, or cpu when there is no GPU)."""
+    import torch
+
+    if torch.cuda.is_available():
+        n = torch.cuda.device_count()
+        dev = info.local_rank % max(n, 1)
+        torch.cuda.set_device(dev)
+        return torch.device("cuda", dev)
+    return torch.device("cpu")
+
+
+def init_process_group(info: RankInfo, backend: Optional[str] = None, timeout_s: int = 600):
+    """Host-side rendezvous (bootstrap, object broadcast, IPC-handle exchange).  On a GPU box the
+    group is NCCL (it is also the measured baseline for gradient reduction); on CPU it is gloo."""
+    import datetime
+
+    import torch
+    import torch.distributed as dist
+
+    if dist.is_initialized():
+        return
+    if backend is None:
+        # one group, two transports: gloo for host objects, NCCL for device tensors
+        backend = "cpu:gloo,cuda:nccl" if torch.cuda.is_available() else "gloo"
+    os.environ.setdefault("MASTER_ADDR", info.master_addr)
+    os.environ.setdefault("MASTER_PORT", str(info.master_port))
+    kw = {}
+    if "nccl" in backend:
+        kw["device_id"] = torch.device("cuda", torch.cuda.current_device())
+    dist.init_process_group(
+        backend=backend, rank=info.rank, world_size=info.world_size,
+        timeout=datetime.timedelta(seconds=timeout_s), **kw)

@@ -1,0 +1,190 @@
+"""The MLP regressor.
+
+``MLP`` is the user-facing ``nn.Module`` with the reference's interface (``MLP()``, ``forward(x)``,
+a ``layers`` ``nn.Sequential`` of Linear/ReLU pairs; ref.py:35-51) generalised to any width list.
+
+``FlatMLP`` is what the trainer actually steps: one flat fp32 buffer for all parameters, one for
+the gradients (the all-reduce bucket; peer-mapped on multi-GPU runs), one for the momentum and, for
+bf16 training, a bf16 shadow copy of the weights that the GEMMs read.  Per-layer tensors are
+views into those buffers.  Flat offsets follow ``model.parameters()`` order of the reference
+(weight, bias per Linear; ref.py:181), each segment padded to 256 bytes so every weight matrix can
+be described by a TMA tensor map and moved with 16-byte vectors.  ``state_dict()`` uses the
+reference's key names (``layers.0.weight`` ...) so a checkpoint loads into the
+reference's own ``MLP``.
+"""
+from __future__ import annotations
+
+from collections import OrderedDict
+from dataclasses import dataclass
+from typing import Dict, List, Optional, Sequence
+
+import torch
+from torch import nn
+
+ALIGN_ELEMS = 128   # segment alignment in elements: 512 B in fp32, 256 B in bf16
+
+
+class MLP(nn.Module):
+    """Multilayer perceptron for regression; ``MLP()`` is the reference's 2-3-1 net (ref.py:41-45)."""
+
+    def __init__(self, sizes: Sequence[int] = (2, 3, 1)):
+        super().__init__()
+        mods: List[nn.Module] = []
+        for i in range(len(sizes) - 1):
+            mods.append(nn.Linear(sizes[i], sizes[i + 1]))
+            if i < len(sizes) - 2:
+                mods.append(nn.ReLU())
+        self.layers = nn.Sequential(*mods)
+        self.sizes = tuple(sizes)
+
+    def forward(self, x):
+        return self.layers(x)
+
+
+@dataclass(frozen=True)
+class Segment:
+    key: str
+    layer: int
+    kind: str        # "weight" | "bias"
+    offset: int      # elements into the flat buffers
+    numel: int
+    shape: tuple
+
+
+def _round_up(x: int, m: int) -> int:
+    return (x + m - 1) // m * m
+
+
+class MLPSpec:
+    def __init__(self, sizes: Sequence[int]):
+        if len(sizes) < 2:
+            raise ValueError("an MLP needs at least an input and an output size")
+        self.sizes = tuple(int(s) for s in sizes)
+        self.num_layers = len(self.sizes) - 1
+        segs: List[Segment] = []
+        off = 0
+        for l in range(self.num_layers):
+            fan_in, fan_out = self.sizes[l], self.sizes[l + 1]
+            for kind, shape in (("weight", (fan_out, fan_in)), ("bias", (fan_out,))):
+                n = 1
+                for s in shape:
+                    n *= s
+                segs.append(Segment(f"layers.{2 * l}.{kind}", l, kind, off, n, shape))
+                off = _round_up(off + n, ALIGN_ELEMS)
+        self.segments = tuple(segs)
+        self.flat_numel = off
+        self.num_params = sum(s.numel for s in segs)
+
+    def layer_segments(self, l: int):
+        return self.segments[2 * l], self.segments[2 * l + 1]
+
+    def layer_span(self, l: int):
+        """[start, stop) elements of layer ``l`` (weight + bias + padding): the per-layer bucket."""
+        start = self.segments[2 * l].offset
+        stop = self.segments[2 * l + 2].offset if l + 1 < self.num_layers else self.flat_numel
+        return start, stop
+
+    def is_tiny(self, limit: int = 64) -> bool:
+        """True when every dimension is too small to feed a tensor-core tile (the reference's
+        2-3-1 net): such models run on the fused SIMT kernel instead of the tcgen05 GEMMs."""
+        return max(self.sizes) <= limit
+
+
+class FlatMLP:
+    def __init__(self, spec: MLPSpec, device, dtype: str = "fp32",
+                 grads: Optional[torch.Tensor] = None, shadow: Optional[torch.Tensor] = None,
+                 params: Optional[torch.Tensor] = None):
+        self.spec, self.device, self.dtype = spec, torch.device(device), dtype
+        n = spec.flat_numel
+        self.params = params if params is not None else torch.zeros(n, dtype=torch.float32, device=device)
+        self.momentum = torch.zeros(n, dtype=torch.float32, device=device)
+        gdt = torch.bfloat16 if dtype == "bf16" else torch.float32
+        self.grads = grads if grads is not None else torch.zeros(n, dtype=gdt, device=device)
+        self.shadow = None
+        if dtype == "bf16":
+            self.shadow = shadow if shadow is not None else torch.zeros(n, dtype=torch.bfloat16, device=device)
+        self.step_count = 0
+
+    # ---- views ----
+    def _view(self, flat: torch.Tensor, seg: Segment) -> torch.Tensor:
+        return flat[seg.offset:seg.offset + seg.numel].view(seg.shape)
+
+    def weight(self, l: int, flat: Optional[torch.Tensor] = None) -> torch.Tensor:
+        return self._view(self.params if flat is None else flat, self.spec.segments[2 * l])
+
+    def bias(self, l: int, flat: Optional[torch.Tensor] = None) -> torch.Tensor:
+        return self._view(self.params if flat is None else flat, self.spec.segments[2 * l + 1])
+
+    def compute_weight(self, l: int) -> torch.Tensor:
+        """The tensor the GEMMs read: the bf16 shadow in bf16 mode, else the fp32 master."""
+        return self.weight(l, self.shadow if self.shadow is not None else self.params)
+
+    def compute_bias(self, l: int) -> torch.Tensor:
+        return self.bias(l, self.params)
+
+    # ---- initialisation ----
+    def init_like_reference(self, seed: int = 0) -> None:
+        """``torch.manual_seed(seed)`` then ``nn.Linear`` default init on the CPU, in module order -
+        bit-identical to what root creates at ref.py:69,84 and broadcasts at ref.py:87."""
+        gen_state = torch.random.get_rng_state()
+        try:
+            torch.manual_seed(seed)
+            ref = MLP(self.spec.sizes)
+        finally:
+            torch.random.set_rng_state(gen_state)
+        self.load_state_dict(ref.state_dict())
+
+    def init_on_device(self, seed: int = 0) -> None:
+        """Same distribution (uniform +-1/sqrt(fan_in) for weight and bias), generated on the
+        device: for billion-parameter models where a CPU init would dominate start-up."""
+        g = torch.Generator(device=self.device).manual_seed(seed)
+        for seg in self.spec.segments:
+            fan_in = self.spec.sizes[seg.layer]
+            bound = 1.0 / (fan_in ** 0.5)
+            v = self._view(self.params, seg)
+            v.copy_((torch.rand(seg.shape, generator=g, device=self.device) * 2 - 1) * bound)
+        self.sync_shadow()
+
+    def sync_shadow(self) -> None:
+        if self.shadow is not None:
+            self.shadow.copy_(self.params)
+
+    # ---- state dict (reference key names) ----
+    def state_dict(self) -> "OrderedDict[str, torch.Tensor]":
+        out = OrderedDict()
+        for seg in self.spec.segments:
+            out[seg.key] = self._view(self.params, seg).detach().to("cpu", copy=True)
+        return out
+
+    def load_state_dict(self, sd: Dict[str, torch.Tensor]) -> None:
+        keys = [s.key for s in self.spec.segments]
+        missing = [k for k in keys if k not in sd]
+        extra = [k for k in sd if k not in keys]
+        if missing or extra:
+            raise KeyError(f"state_dict mismatch: missing={missing} unexpected={extra}")
+        for seg in self.spec.segments:
+            t = sd[seg.key]
+            if tuple(t.shape) != tuple(seg.shape):
+                raise ValueError(f"{seg.key}: shape {tuple(t.shape)} != {seg.shape}")
+            self._view(self.params, seg).copy_(t.to(self.device, torch.float32))
+        self.sync_shadow()
+
+    def momentum_state(self) -> "OrderedDict[str, torch.Tensor]":
+        return OrderedDict((s.key, self._view(self.momentum, s).detach().to("cpu", copy=True))
+                           for s in self.spec.segments)
+
+    def load_momentum_state(self, sd: Dict[str, torch.Tensor]) -> None:
+        for seg in self.spec.segments:
+            self._view(self.momentum, seg).copy_(sd[seg.key].to(self.device, torch.float32))
+
+    def as_module(self) -> MLP:
+        m = MLP(self.spec.sizes)
+        m.load_state_dict(self.state_dict())
+        return m
+
+    def fingerprint(self) -> int:
+        """Order-sensitive 64-bit hash of the parameter bytes (replica-equality checks)."""
+        b = self.params.detach().to("cpu").contiguous().view(torch.uint8).numpy().tobytes()
+        import hashlib
+
+        return int.from_bytes(hashlib.blake2b(b, digest_size=8).digest(), "little")

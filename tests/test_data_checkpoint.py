@@ -1,0 +1,129 @@
+import numpy as np
+import pytest
+import torch
+from sklearn.preprocessing import StandardScaler
+
+from b200dp import MLP, RegressionDataset
+from b200dp.checkpoint import load_checkpoint, save_checkpoint
+from b200dp.config import TrainConfig
+from b200dp.data import load_shard, make_randn_rows, make_regression_xy, standard_scale
+from b200dp.engine import Trainer
+from b200dp.models.mlp import FlatMLP, MLPSpec
+from b200dp.parallel.comm import SingleComm, run_threads
+
+
+def test_dataset_anchor_rows():                           # SURVEY §4.3 data sanity anchor
+    xy = make_regression_xy()
+    assert xy.shape == (16, 3) and xy.dtype == np.float64
+    np.testing.assert_allclose(xy[0], [1.5230, 0.6477, 82.1004], atol=5e-4)
+    np.testing.assert_allclose(xy[1], [-0.2258, 1.4656, 5.2281], atol=5e-4)
+
+
+def test_standard_scale_equals_sklearn():
+    x = np.random.RandomState(0).randn(11, 4) * 3 + 1
+    x[:, 2] = 7.0                                         # zero-variance column
+    np.testing.assert_allclose(standard_scale(x), StandardScaler().fit_transform(x), atol=1e-12)
+
+
+def test_regression_dataset_interface():                  # ref.py:12-30
+    xy = make_regression_xy()
+    ds = RegressionDataset(xy[:, :2], xy[:, 2])
+    assert len(ds) == 16 and ds.X.dtype == torch.float64
+    x0, y0 = ds[0]
+    assert x0.shape == (2,) and y0.shape == ()
+    np.testing.assert_allclose(ds.X.mean(0).numpy(), 0, atol=1e-12)
+    raw = RegressionDataset(xy[:, :2], xy[:, 2], scale_data=False)
+    np.testing.assert_array_equal(raw.X.numpy(), xy[:, :2])
+    # tensors are accepted (the reference silently breaks on them)
+    assert len(RegressionDataset(torch.from_numpy(xy[:, :2]), torch.from_numpy(xy[:, 2]))) == 16
+
+
+@pytest.mark.parametrize("world", [2, 3, 5])
+def test_scatter_and_local_shards_agree(world):
+    def fn(comm):
+        a = load_shard(TrainConfig(data_dist="scatter"), comm)
+        b = load_shard(TrainConfig(data_dist="local"), comm)
+        torch.testing.assert_close(a.x, b.x)
+        torch.testing.assert_close(a.y, b.y)
+        return a.rows, a.start
+
+    res = run_threads(world, fn)
+    assert sum(r[0] for r in res) == 16
+    assert [r[1] for r in res] == list(np.cumsum([0] + [r[0] for r in res])[:-1])
+
+
+def test_randn_rows_are_world_size_independent():
+    full = make_randn_rows(0, 10000, 7, 0.1, seed=3)
+    part = make_randn_rows(4090, 8200, 7, 0.1, seed=3)
+    np.testing.assert_array_equal(full[4090:8200], part)
+
+
+def test_flat_layout_alignment_and_keys():
+    spec = MLPSpec([2, 3, 1])
+    assert [s.key for s in spec.segments] == ["layers.0.weight", "layers.0.bias", "layers.2.weight",
+                                              "layers.2.bias"]
+    assert spec.num_params == 13
+    assert all(s.offset % 128 == 0 for s in spec.segments)
+    big = MLPSpec([12288, 4096, 4096, 4096, 4096, 1])
+    assert abs(big.num_params - 100.7e6) < 0.1e6
+
+
+def test_seed0_init_matches_reference_values():
+    flat = FlatMLP(MLPSpec([2, 3, 1]), "cpu")
+    flat.init_like_reference(0)
+    sd = flat.state_dict()
+    torch.testing.assert_close(sd["layers.0.bias"], torch.tensor([-0.0140100336, 0.5606575012, -0.0627515167]))
+    torch.testing.assert_close(sd["layers.2.bias"], torch.tensor([-0.5515707135]))
+    torch.manual_seed(0)
+    ref = MLP()
+    for k, v in ref.state_dict().items():
+        assert torch.equal(sd[k], v)
+
+
+def test_checkpoint_roundtrip_and_loads_into_plain_module(tmp_path):
+    path = str(tmp_path / "ck.pt")
+    t = Trainer(TrainConfig(quiet=True, nepochs=2, checkpoint=path))
+    t.train()
+    payload = torch.load(path, weights_only=False)
+    assert list(payload["model"].keys()) == ["layers.0.weight", "layers.0.bias", "layers.2.weight",
+                                             "layers.2.bias"]
+    assert all(v.dtype == torch.float32 for v in payload["model"].values())
+    assert payload["epoch"] == 2
+    # loads into a stock module shaped like the reference's MLP (ref.py:41-45)
+    m = MLP()
+    m.load_state_dict(payload["model"])
+    x = torch.randn(4, 2)
+    torch.testing.assert_close(m(x), t.predict(x))
+
+
+def test_resume_is_exact(tmp_path):
+    path = str(tmp_path / "ck.pt")
+    full = Trainer(TrainConfig(quiet=True, nepochs=6))
+    full.train()
+    a = Trainer(TrainConfig(quiet=True, nepochs=3, checkpoint=path))
+    a.train()
+    b = Trainer(TrainConfig(quiet=True, nepochs=6, resume=path))
+    assert b.start_epoch == 3
+    b.train()
+    assert b.flat.fingerprint() == full.flat.fingerprint()
+    assert [h["loss"] for h in b.history] == [h["loss"] for h in full.history[3:]]
+
+
+def test_checkpoint_size_mismatch(tmp_path):
+    path = str(tmp_path / "ck.pt")
+    flat = FlatMLP(MLPSpec([2, 3, 1]), "cpu")
+    save_checkpoint(path, flat, 0, {})
+    with pytest.raises(ValueError):
+        load_checkpoint(path, FlatMLP(MLPSpec([2, 4, 1]), "cpu"))
+
+
+def test_validation_and_jsonl(tmp_path):
+    log = str(tmp_path / "m.jsonl")
+    t = Trainer(TrainConfig(quiet=True, nepochs=2, n_samples=32, val_frac=0.25, log_jsonl=log,
+                            data_dist="local"), SingleComm())
+    h = t.train()
+    t.close()
+    assert "val_loss" in h[0] and h[0]["val_loss"] > 0
+    import json
+    recs = [json.loads(l) for l in open(log)]
+    assert len(recs) == 2 and "samples_per_s" in recs[0] and "global_loss" in recs[0]

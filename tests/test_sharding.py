@@ -1,0 +1,46 @@
+import pytest
+
+from b200dp.parallel.sharding import (element_counts, grad_weights, shard_counts, shard_displs,
+                                      shard_range)
+
+
+@pytest.mark.parametrize("rows,world", [(16, 1), (16, 2), (16, 3), (16, 5), (16, 7), (16, 8), (16, 16),
+                                        (16, 20), (0, 4), (1, 3), (1000003, 8)])
+def test_counts_cover_all_rows_contiguously(rows, world):
+    c = shard_counts(rows, world)
+    d = shard_displs(c)
+    assert sum(c) == rows and len(c) == world
+    assert max(c) - min(c) <= 1
+    # first `residue` ranks own the extra row (ref.py:117)
+    res = rows % world
+    assert all(c[p] == rows // world + 1 for p in range(res))
+    assert all(c[p] == rows // world for p in range(res, world))
+    for r in range(world):
+        assert shard_range(rows, world, r) == (d[r], d[r] + c[r])
+    assert d == [sum(c[:p]) for p in range(world)]         # ref.py:121
+
+
+def test_reference_example_16_rows_3_ranks():
+    assert shard_counts(16, 3) == [6, 5, 5]
+    assert shard_counts(16, 5) == [4, 3, 3, 3, 3]
+    cnt, dsp = element_counts(16, 3, 3)
+    assert cnt == [18, 15, 15] and dsp == [0, 18, 33]
+
+
+def test_counts_exceed_int8_range():
+    # the reference stores w*count in int8 (ref.py:118); ours must not overflow
+    cnt, _ = element_counts(100000, 3, 2)
+    assert cnt == [150000, 150000]
+
+
+def test_grad_weights():
+    assert grad_weights(16, 4) == [0.25] * 4
+    w = grad_weights(16, 3, "samples")
+    assert w == [6 / 16, 5 / 16, 5 / 16] and abs(sum(w) - 1) < 1e-12
+    with pytest.raises(ValueError):
+        grad_weights(16, 3, "bogus")
+
+
+def test_bad_world():
+    with pytest.raises(ValueError):
+        shard_counts(4, 0)
