@@ -1,0 +1,59 @@
+"""Python face of the tcgen05 Linear GEMMs (``csrc/gemm_tcgen05.cu``)."""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+
+from . import _lib
+
+
+def _check_bf16(t: torch.Tensor, name: str):
+    if t.dtype != torch.bfloat16 or not t.is_cuda or t.dim() != 2 or t.stride(1) != 1:
+        raise ValueError(f"{name} must be a 2-D bf16 CUDA tensor with unit inner stride")
+
+
+def gemm(A: torch.Tensor, B: torch.Tensor, out: torch.Tensor, *, a_mn_major=False, b_mn_major=False,
+         bias: Optional[torch.Tensor] = None, relu=False, mask_src: Optional[torch.Tensor] = None,
+         tile_n=0, max_ctas=0, stream=None) -> torch.Tensor:
+    """``out[M,N] = epi(A[M,K] @ B[N,K]^T)``.  ``a_mn_major``: A is given as its transpose ``[K,M]``;
+    ``b_mn_major``: B is given as ``[K,N]``."""
+    _check_bf16(A, "A")
+    _check_bf16(B, "B")
+    M, K = (A.shape[1], A.shape[0]) if a_mn_major else (A.shape[0], A.shape[1])
+    N, Kb = (B.shape[1], B.shape[0]) if b_mn_major else (B.shape[0], B.shape[1])
+    if K != Kb:
+        raise ValueError(f"reduction sizes differ: {K} vs {Kb}")
+    if tuple(out.shape) != (M, N) or out.stride(1) != 1 or out.dtype not in (torch.bfloat16, torch.float32):
+        raise ValueError("out must be [M,N] bf16/fp32 with unit inner stride")
+    a = _lib.GemmArgs(M=M, N=N, K=K, A=A.data_ptr(), lda=A.stride(0), a_mn_major=int(a_mn_major),
+                      B=B.data_ptr(), ldb=B.stride(0), b_mn_major=int(b_mn_major),
+                      D=out.data_ptr(), ldd=out.stride(0), d_fp32=int(out.dtype == torch.float32),
+                      bias=_lib.ptr(bias), relu=int(relu), mask_src=_lib.ptr(mask_src),
+                      ldmask=mask_src.stride(0) if mask_src is not None else 0,
+                      tile_n=tile_n, max_ctas=max_ctas)
+    _lib.check(_lib.lib().b200dp_gemm_bf16(C.byref(a), _lib.stream_ptr(stream)))
+    _lib.count()
+    return out
+
+
+def linear_fwd(x, w, bias, relu, out=None, **kw):
+    """``relu?(x @ w.T + bias)``; x [M,K] bf16, w [N,K] bf16, bias fp32 [N]."""
+    if out is None:
+        out = torch.empty(x.shape[0], w.shape[0], dtype=torch.bfloat16, device=x.device)
+    return gemm(x, w, out, bias=bias, relu=relu, **kw)
+
+
+def linear_dgrad(dy, w, relu_src, out=None, **kw):
+    """``(dy @ w) * [relu_src > 0]``; dy [M,N] bf16, w [N,K] bf16 (used MN-major, no transpose copy)."""
+    if out is None:
+        out = torch.empty(dy.shape[0], w.shape[1], dtype=torch.bfloat16, device=dy.device)
+    return gemm(dy, w, out, b_mn_major=True, mask_src=relu_src, **kw)
+
+
+def linear_wgrad(dy, x, out=None, **kw):
+    """``dy.T @ x`` -> [N,K]; both operands used MN-major straight from their row-major storage."""
+    if out is None:
+        out = torch.empty(dy.shape[1], x.shape[1], dtype=torch.float32, device=dy.device)
+    return gemm(dy, x, out, a_mn_major=True, b_mn_major=True, **kw)
