@@ -1,0 +1,380 @@
+// Loss and narrow-output ("head") kernels.
+//
+//  * mse_loss_grad     - fused MSE loss + gradient: one pass over the predictions writes the scalar
+//                        loss and dY = 2 (Yhat - Y) / numel  (aten::mse_loss + MseLossBackward,
+//                        ref.py:173,176).  Deterministic two-stage reduction through scratch memory.
+//  * head_fwd_mse      - last Linear layer when it has very few outputs (the regression head,
+//                        e.g. 4096 -> 1): a GEMV per row on CUDA cores (tensor cores cannot be fed by
+//                        N = 1), fused with bias, the MSE loss and dY (ref.py:44,170,173,176).
+//  * head_bwd          - backward of that layer in ONE pass over its input H: dH = (dY W) * [H>0]
+//                        (bf16) and per-row-strip partial sums of dW = dY^T H and db = sum dY.
+//  * colsum / reduce_partials - bias gradient of the GEMM layers (db = column sums of dY) and the
+//                        fixed-order reduction of any [strips][n] partial buffer.
+#include "common.cuh"
+
+namespace b200dp {
+namespace {
+
+constexpr int kRedThreads = 256;
+
+// block-wide sum; result valid in thread 0
+__device__ __forceinline__ float block_sum(float v, float* red) {
+  v = warp_sum(v);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  float s = 0.0f;
+  if (threadIdx.x == 0)
+    for (int w = 0; w < (blockDim.x >> 5); ++w) s += red[w];
+  return s;
+}
+
+// Publishes this block's partial, and lets the last block to arrive add all partials in block
+// order (bit-reproducible) and write scale * sum to `out`.  scratch = [ticket(u32) pad to 256 B][partials].
+__device__ __forceinline__ void finish_scalar(float block_val, float scale, float* out, float* partials,
+                                              unsigned int* ticket, bool* is_last_smem) {
+  if (threadIdx.x == 0) {
+    partials[blockIdx.x] = block_val;
+    __threadfence();
+    const unsigned int prev = atomicAdd(ticket, 1u);
+    *is_last_smem = (prev == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (*is_last_smem && threadIdx.x == 0) {
+    __threadfence();
+    float s = 0.0f;
+    for (unsigned int b = 0; b < gridDim.x; ++b) s += partials[b];
+    *out = s * scale;
+    *ticket = 0;      // the scratch is reusable by the next launch on the stream
+  }
+}
+
+template <bool PRED_BF16, bool DY_BF16>
+__global__ void __launch_bounds__(kRedThreads)
+mse_kernel(const void* __restrict__ pred, const float* __restrict__ target, long long n, float inv_n,
+           void* __restrict__ dy, float* __restrict__ loss, float* partials, unsigned int* ticket) {
+  __shared__ float red[kRedThreads / 32];
+  __shared__ bool is_last;
+  float acc = 0.0f;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const float p = PRED_BF16 ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(pred)[i])
+                              : reinterpret_cast<const float*>(pred)[i];
+    const float d = p - target[i];
+    acc = fmaf(d, d, acc);
+    const float g = 2.0f * d * inv_n;
+    if (DY_BF16) reinterpret_cast<__nv_bfloat16*>(dy)[i] = __float2bfloat16_rn(g);
+    else reinterpret_cast<float*>(dy)[i] = g;
+  }
+  const float b = block_sum(acc, red);
+  finish_scalar(b, inv_n, loss, partials, ticket, &is_last);
+}
+
+// ---- head forward: one warp per row ----
+template <int NOUT>
+__global__ void __launch_bounds__(kRedThreads)
+head_fwd_kernel(const __nv_bfloat16* __restrict__ H, long long ldh, const __nv_bfloat16* __restrict__ W,
+                const float* __restrict__ bias, const float* __restrict__ target, int rows, int K,
+                float inv_n, float* __restrict__ yhat, float* __restrict__ dy, float* __restrict__ loss,
+                float* partials, unsigned int* ticket) {
+  __shared__ float red[kRedThreads / 32];
+  __shared__ bool is_last;
+  const int lane = threadIdx.x & 31;
+  const int warps_per_block = blockDim.x >> 5;
+  const int gw = blockIdx.x * warps_per_block + (threadIdx.x >> 5);
+  const int nw = gridDim.x * warps_per_block;
+  float acc_loss = 0.0f;
+  for (int r = gw; r < rows; r += nw) {
+    const __nv_bfloat16* h = H + (long long)r * ldh;
+    float s[NOUT];
+#pragma unroll
+    for (int o = 0; o < NOUT; ++o) s[o] = 0.0f;
+    for (int k = lane * 8; k < K; k += 256) {
+      const uint4 hv = __ldg(reinterpret_cast<const uint4*>(h + k));
+      const uint32_t hw[4] = {hv.x, hv.y, hv.z, hv.w};
+#pragma unroll
+      for (int o = 0; o < NOUT; ++o) {
+        const uint4 wv = __ldg(reinterpret_cast<const uint4*>(W + (long long)o * K + k));
+        const uint32_t ww[4] = {wv.x, wv.y, wv.z, wv.w};
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          s[o] = fmaf(bf16_lo(hw[q]), bf16_lo(ww[q]), s[o]);
+          s[o] = fmaf(bf16_hi(hw[q]), bf16_hi(ww[q]), s[o]);
+        }
+      }
+    }
+#pragma unroll
+    for (int o = 0; o < NOUT; ++o) s[o] = warp_sum(s[o]);
+    if (lane == 0) {
+#pragma unroll
+      for (int o = 0; o < NOUT; ++o) {
+        const float p = s[o] + bias[o];
+        const float d = p - target[(long long)r * NOUT + o];
+        yhat[(long long)r * NOUT + o] = p;
+        dy[(long long)r * NOUT + o] = 2.0f * d * inv_n;
+        acc_loss = fmaf(d, d, acc_loss);
+      }
+    }
+  }
+  const float b = block_sum(acc_loss, red);
+  finish_scalar(b, inv_n, loss, partials, ticket, &is_last);
+}
+
+// ---- head backward: block = (row strip, 2048-column chunk); thread owns 8 columns ----
+constexpr int kHeadBwdThreads = 256;
+constexpr int kHeadBwdCols = kHeadBwdThreads * 8;
+
+template <int NOUT>
+__global__ void __launch_bounds__(kHeadBwdThreads)
+head_bwd_kernel(const float* __restrict__ dy, const __nv_bfloat16* __restrict__ W,
+                const __nv_bfloat16* __restrict__ H, long long ldh, int rows, int K, int rows_per_strip,
+                __nv_bfloat16* __restrict__ dH, long long lddh, float* __restrict__ partials) {
+  // partials layout: [strip][NOUT][K + 1]; column K holds the bias-gradient partial
+  const int strip = blockIdx.x;
+  const int k0 = blockIdx.y * kHeadBwdCols + threadIdx.x * 8;
+  const int r_begin = strip * rows_per_strip;
+  const int r_end = min(rows, r_begin + rows_per_strip);
+  const bool active = k0 < K;
+  float w[NOUT][8];
+  float acc[NOUT][8];
+#pragma unroll
+  for (int o = 0; o < NOUT; ++o) {
+    uint4 wv = make_uint4(0, 0, 0, 0);
+    if (active) wv = __ldg(reinterpret_cast<const uint4*>(W + (long long)o * K + k0));
+    const uint32_t ww[4] = {wv.x, wv.y, wv.z, wv.w};
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      w[o][2 * q] = bf16_lo(ww[q]);
+      w[o][2 * q + 1] = bf16_hi(ww[q]);
+      acc[o][2 * q] = acc[o][2 * q + 1] = 0.0f;
+    }
+  }
+  float bacc[NOUT];
+#pragma unroll
+  for (int o = 0; o < NOUT; ++o) bacc[o] = 0.0f;
+
+  for (int r = r_begin; r < r_end; ++r) {
+    float g[NOUT];
+#pragma unroll
+    for (int o = 0; o < NOUT; ++o) g[o] = __ldg(dy + (long long)r * NOUT + o);
+    if (blockIdx.y == 0 && threadIdx.x == 0) {
+#pragma unroll
+      for (int o = 0; o < NOUT; ++o) bacc[o] += g[o];
+    }
+    if (!active) continue;
+    const uint4 hv = __ldg(reinterpret_cast<const uint4*>(H + (long long)r * ldh + k0));
+    const uint32_t hw[4] = {hv.x, hv.y, hv.z, hv.w};
+    float h[8];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) { h[2 * q] = bf16_lo(hw[q]); h[2 * q + 1] = bf16_hi(hw[q]); }
+    float dh[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) dh[j] = 0.0f;
+#pragma unroll
+    for (int o = 0; o < NOUT; ++o) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        dh[j] = fmaf(g[o], w[o][j], dh[j]);
+        acc[o][j] = fmaf(g[o], h[j], acc[o][j]);
+      }
+    }
+    if (dH != nullptr) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) dh[j] = h[j] > 0.0f ? dh[j] : 0.0f;
+      uint4 o4;
+      o4.x = pack_bf16x2(dh[0], dh[1]); o4.y = pack_bf16x2(dh[2], dh[3]);
+      o4.z = pack_bf16x2(dh[4], dh[5]); o4.w = pack_bf16x2(dh[6], dh[7]);
+      *reinterpret_cast<uint4*>(dH + (long long)r * lddh + k0) = o4;
+    }
+  }
+  float* my = partials + (long long)strip * NOUT * (K + 1);
+  if (active) {
+#pragma unroll
+    for (int o = 0; o < NOUT; ++o) {
+      // (K+1)-float rows are not 16-byte aligned in general: scalar stores
+      float* d = my + (long long)o * (K + 1) + k0;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) d[j] = acc[o][j];
+    }
+  }
+  if (blockIdx.y == 0 && threadIdx.x == 0) {
+#pragma unroll
+    for (int o = 0; o < NOUT; ++o) my[(long long)o * (K + 1) + K] = bacc[o];
+  }
+}
+
+// out[j] = sum_s partials[s][j] (fixed order), fp32 or bf16 output; segment-aware copy so one
+// launch can scatter "[NOUT][K+1]" head partials into the separate weight / bias gradient slots.
+template <bool OUT_BF16>
+__global__ void reduce_partials_kernel(const float* __restrict__ partials, int strips, long long n, void* out) {
+  const long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n) return;
+  float s = 0.0f;
+  for (int t = 0; t < strips; ++t) s += partials[(long long)t * n + j];
+  if (OUT_BF16) reinterpret_cast<__nv_bfloat16*>(out)[j] = __float2bfloat16_rn(s);
+  else reinterpret_cast<float*>(out)[j] = s;
+}
+
+template <bool OUT_BF16>
+__global__ void head_reduce_kernel(const float* __restrict__ partials, int strips, int nout, int K, void* dW,
+                                   void* db) {
+  const long long n = (long long)nout * (K + 1);
+  const long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n) return;
+  float s = 0.0f;
+  for (int t = 0; t < strips; ++t) s += partials[(long long)t * n + j];
+  const int o = int(j / (K + 1)), k = int(j % (K + 1));
+  void* dst = k < K ? dW : db;
+  const long long idx = k < K ? (long long)o * K + k : o;
+  if (OUT_BF16) reinterpret_cast<__nv_bfloat16*>(dst)[idx] = __float2bfloat16_rn(s);
+  else reinterpret_cast<float*>(dst)[idx] = s;
+}
+
+// column sums of a bf16 [rows, n] matrix over a strip of rows -> partials[strip][n]
+__global__ void __launch_bounds__(256)
+colsum_kernel(const __nv_bfloat16* __restrict__ A, long long lda, int rows, int n, int rows_per_strip,
+              float* __restrict__ partials) {
+  const int c0 = (blockIdx.y * blockDim.x + threadIdx.x) * 8;
+  if (c0 >= n) return;
+  const int r_begin = blockIdx.x * rows_per_strip;
+  const int r_end = min(rows, r_begin + rows_per_strip);
+  float acc[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j] = 0.0f;
+  for (int r = r_begin; r < r_end; ++r) {
+    const uint4 v = __ldg(reinterpret_cast<const uint4*>(A + (long long)r * lda + c0));
+    const uint32_t u[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int q = 0; q < 4; ++q) { acc[2 * q] += bf16_lo(u[q]); acc[2 * q + 1] += bf16_hi(u[q]); }
+  }
+  float* dst = partials + (long long)blockIdx.x * n + c0;
+  *reinterpret_cast<float4*>(dst) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+  *reinterpret_cast<float4*>(dst + 4) = make_float4(acc[4], acc[5], acc[6], acc[7]);
+}
+
+inline int reduce_grid(long long n) {
+  long long g = (n + kRedThreads - 1) / kRedThreads;
+  const long long cap = 4ll * sm_count();
+  return int(g < 1 ? 1 : (g > cap ? cap : g));
+}
+
+}  // namespace
+}  // namespace b200dp
+
+using namespace b200dp;
+
+extern "C" long long b200dp_mse_scratch_bytes(long long numel) { return 256 + 4ll * reduce_grid(numel); }
+
+extern "C" int b200dp_mse_loss_grad(const void* pred, int pred_bf16, const float* target, long long numel,
+                                    void* dy, int dy_bf16, float* loss, void* scratch, long long scratch_bytes,
+                                    void* stream) {
+  B200DP_REQUIRE(pred && target && dy && loss && scratch, "mse: null pointer");
+  B200DP_REQUIRE(numel >= 1, "mse: numel must be >= 1");
+  const int grid = reduce_grid(numel);
+  B200DP_REQUIRE(scratch_bytes >= 256 + 4ll * grid, "mse: scratch too small (%lld < %lld bytes)", scratch_bytes,
+                 256 + 4ll * grid);
+  unsigned int* ticket = reinterpret_cast<unsigned int*>(scratch);
+  float* partials = reinterpret_cast<float*>(reinterpret_cast<char*>(scratch) + 256);
+  const float inv_n = 1.0f / float(numel);
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+#define LAUNCH(PB, DB) mse_kernel<PB, DB><<<grid, kRedThreads, 0, s>>>(pred, target, numel, inv_n, dy, loss, partials, ticket)
+  if (pred_bf16 && dy_bf16) LAUNCH(true, true);
+  else if (pred_bf16) LAUNCH(true, false);
+  else if (dy_bf16) LAUNCH(false, true);
+  else LAUNCH(false, false);
+#undef LAUNCH
+  B200DP_CUDA_OK(cudaGetLastError());
+  return B200DP_OK;
+}
+
+extern "C" long long b200dp_head_scratch_bytes(int rows, int K, int nout) {
+  const int strips = (rows + 31) / 32;
+  const long long fwd = 256 + 4ll * 4 * sm_count();
+  return fwd + 4ll * strips * nout * (K + 1);
+}
+
+extern "C" int b200dp_head_fwd_mse(const void* H, long long ldh, const void* W, const float* bias,
+                                   const float* target, int rows, int K, int nout, float* yhat, float* dy,
+                                   float* loss, void* scratch, long long scratch_bytes, void* stream) {
+  B200DP_REQUIRE(H && W && bias && target && yhat && dy && loss && scratch, "head_fwd: null pointer");
+  B200DP_REQUIRE(nout >= 1 && nout <= 4, "head_fwd: supports 1..4 outputs (got %d)", nout);
+  B200DP_REQUIRE(K % 8 == 0 && ldh % 8 == 0, "head_fwd: K and ldh must be multiples of 8");
+  B200DP_REQUIRE(rows >= 1, "head_fwd: rows must be >= 1");
+  int grid = (rows + (kRedThreads / 32) - 1) / (kRedThreads / 32);
+  if (grid > 4 * sm_count()) grid = 4 * sm_count();
+  B200DP_REQUIRE(scratch_bytes >= 256 + 4ll * grid, "head_fwd: scratch too small");
+  unsigned int* ticket = reinterpret_cast<unsigned int*>(scratch);
+  float* partials = reinterpret_cast<float*>(reinterpret_cast<char*>(scratch) + 256);
+  const float inv_n = 1.0f / (float(rows) * float(nout));
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  const __nv_bfloat16* h = reinterpret_cast<const __nv_bfloat16*>(H);
+  const __nv_bfloat16* w = reinterpret_cast<const __nv_bfloat16*>(W);
+#define LAUNCH(NO) head_fwd_kernel<NO><<<grid, kRedThreads, 0, s>>>(h, ldh, w, bias, target, rows, K, inv_n, yhat, dy, loss, partials, ticket)
+  switch (nout) {
+    case 1: LAUNCH(1); break;
+    case 2: LAUNCH(2); break;
+    case 3: LAUNCH(3); break;
+    default: LAUNCH(4); break;
+  }
+#undef LAUNCH
+  B200DP_CUDA_OK(cudaGetLastError());
+  return B200DP_OK;
+}
+
+extern "C" int b200dp_head_bwd(const float* dy, const void* W, const void* H, long long ldh, int rows, int K,
+                               int nout, void* dH, long long lddh, void* dW, void* db, int grads_bf16,
+                               void* scratch, long long scratch_bytes, void* stream) {
+  B200DP_REQUIRE(dy && W && H && dW && db && scratch, "head_bwd: null pointer");
+  B200DP_REQUIRE(nout >= 1 && nout <= 4, "head_bwd: supports 1..4 outputs (got %d)", nout);
+  B200DP_REQUIRE(K % 8 == 0 && ldh % 8 == 0 && (dH == nullptr || lddh % 8 == 0),
+                 "head_bwd: K, ldh, lddh must be multiples of 8");
+  const int rows_per_strip = 32;
+  const int strips = (rows + rows_per_strip - 1) / rows_per_strip;
+  const long long fwd = 256 + 4ll * 4 * sm_count();
+  B200DP_REQUIRE(scratch_bytes >= fwd + 4ll * strips * nout * (K + 1), "head_bwd: scratch too small");
+  float* partials = reinterpret_cast<float*>(reinterpret_cast<char*>(scratch) + fwd);
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  dim3 grid(strips, (K + kHeadBwdCols - 1) / kHeadBwdCols);
+  const __nv_bfloat16* w = reinterpret_cast<const __nv_bfloat16*>(W);
+  const __nv_bfloat16* h = reinterpret_cast<const __nv_bfloat16*>(H);
+  __nv_bfloat16* dh = reinterpret_cast<__nv_bfloat16*>(dH);
+#define LAUNCH(NO) head_bwd_kernel<NO><<<grid, kHeadBwdThreads, 0, s>>>(dy, w, h, ldh, rows, K, rows_per_strip, dh, lddh, partials)
+  switch (nout) {
+    case 1: LAUNCH(1); break;
+    case 2: LAUNCH(2); break;
+    case 3: LAUNCH(3); break;
+    default: LAUNCH(4); break;
+  }
+#undef LAUNCH
+  B200DP_CUDA_OK(cudaGetLastError());
+  const long long n = (long long)nout * (K + 1);
+  const int rgrid = int((n + 255) / 256);
+  if (grads_bf16) head_reduce_kernel<true><<<rgrid, 256, 0, s>>>(partials, strips, nout, K, dW, db);
+  else head_reduce_kernel<false><<<rgrid, 256, 0, s>>>(partials, strips, nout, K, dW, db);
+  B200DP_CUDA_OK(cudaGetLastError());
+  return B200DP_OK;
+}
+
+extern "C" long long b200dp_colsum_scratch_bytes(int rows, int n) {
+  const int strips = (rows + 63) / 64;
+  return 4ll * strips * n;
+}
+
+extern "C" int b200dp_colsum_bf16(const void* A, long long lda, int rows, int n, void* out, int out_bf16,
+                                  void* scratch, long long scratch_bytes, void* stream) {
+  B200DP_REQUIRE(A && out && scratch, "colsum: null pointer");
+  B200DP_REQUIRE(n % 8 == 0 && lda % 8 == 0, "colsum: n and lda must be multiples of 8");
+  const int rows_per_strip = 64;
+  const int strips = (rows + rows_per_strip - 1) / rows_per_strip;
+  B200DP_REQUIRE(scratch_bytes >= 4ll * strips * n, "colsum: scratch too small");
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  float* partials = reinterpret_cast<float*>(scratch);
+  dim3 grid(strips, (n / 8 + 255) / 256);
+  colsum_kernel<<<grid, 256, 0, s>>>(reinterpret_cast<const __nv_bfloat16*>(A), lda, rows, n, rows_per_strip,
+                                     partials);
+  B200DP_CUDA_OK(cudaGetLastError());
+  const int rgrid = (n + 255) / 256;
+  if (out_bf16) reduce_partials_kernel<true><<<rgrid, 256, 0, s>>>(partials, strips, n, out);
+  else reduce_partials_kernel<false><<<rgrid, 256, 0, s>>>(partials, strips, n, out);
+  B200DP_CUDA_OK(cudaGetLastError());
+  return B200DP_OK;
+}

@@ -1,0 +1,95 @@
+// Local (single-GPU) optimizer and cast kernels.
+//
+//  * sgd_momentum   - torch.optim.SGD(momentum) semantics of ref.py:91,211 in one pass over flat
+//                     buffers: g' = g * scale;  buf = first ? g' : mu*buf + g';  p -= lr*buf;
+//                     optionally refreshes the bf16 shadow weights the GEMMs read.  Used when the
+//                     world has one rank, and after the NCCL all-reduce baseline.  The multi-GPU
+//                     product path is the fused kernel in allreduce_sgd.cu.
+//  * cast_f32_bf16  - one-time input / weight conversion (the reference's per-step .float() cast,
+//                     ref.py:159, becomes a load-time cast).
+#include "common.cuh"
+
+namespace b200dp {
+namespace {
+
+template <bool GRAD_BF16>
+__global__ void __launch_bounds__(256)
+sgd_kernel(float* __restrict__ p, const void* __restrict__ g, float* __restrict__ m,
+           __nv_bfloat16* __restrict__ shadow, long long n4, float lr, float mu, float scale, int first) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+    float4 gv;
+    if (GRAD_BF16) {
+      const uint2 u = reinterpret_cast<const uint2*>(g)[i];
+      gv = make_float4(bf16_lo(u.x), bf16_hi(u.x), bf16_lo(u.y), bf16_hi(u.y));
+    } else {
+      gv = reinterpret_cast<const float4*>(g)[i];
+    }
+    gv.x *= scale; gv.y *= scale; gv.z *= scale; gv.w *= scale;
+    float4 mv;
+    if (first) mv = gv;
+    else {
+      mv = reinterpret_cast<float4*>(m)[i];
+      mv.x = fmaf(mu, mv.x, gv.x); mv.y = fmaf(mu, mv.y, gv.y);
+      mv.z = fmaf(mu, mv.z, gv.z); mv.w = fmaf(mu, mv.w, gv.w);
+    }
+    reinterpret_cast<float4*>(m)[i] = mv;
+    float4 pv = reinterpret_cast<float4*>(p)[i];
+    pv.x -= lr * mv.x; pv.y -= lr * mv.y; pv.z -= lr * mv.z; pv.w -= lr * mv.w;
+    reinterpret_cast<float4*>(p)[i] = pv;
+    if (shadow) reinterpret_cast<uint2*>(shadow)[i] = make_uint2(pack_bf16x2(pv.x, pv.y), pack_bf16x2(pv.z, pv.w));
+  }
+}
+
+__global__ void __launch_bounds__(256)
+cast_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, long long n) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const long long n4 = n >> 2;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+    const float4 v = reinterpret_cast<const float4*>(src)[i];
+    reinterpret_cast<uint2*>(dst)[i] = make_uint2(pack_bf16x2(v.x, v.y), pack_bf16x2(v.z, v.w));
+  }
+  for (long long i = (n4 << 2) + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+    dst[i] = __float2bfloat16_rn(src[i]);
+}
+
+inline int ew_grid(long long n) {
+  long long g = (n + 255) / 256;
+  const long long cap = 8ll * sm_count();
+  return int(g < 1 ? 1 : (g > cap ? cap : g));
+}
+
+}  // namespace
+}  // namespace b200dp
+
+using namespace b200dp;
+
+extern "C" int b200dp_sgd_momentum(float* params, const void* grads, int grads_bf16, float* momentum,
+                                   void* shadow_bf16, long long n, float lr, float mu, float grad_scale,
+                                   int first_step, void* stream) {
+  B200DP_REQUIRE(params && grads && momentum, "sgd: null pointer");
+  B200DP_REQUIRE(n % 4 == 0, "sgd: n must be a multiple of 4 (flat buffers are padded)");
+  B200DP_REQUIRE(((uintptr_t)params & 15) == 0 && ((uintptr_t)momentum & 15) == 0 &&
+                     ((uintptr_t)grads & (grads_bf16 ? 7 : 15)) == 0,
+                 "sgd: buffers must be 16-byte aligned");
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  const long long n4 = n / 4;
+  const int grid = ew_grid(n4);
+  if (grads_bf16)
+    sgd_kernel<true><<<grid, 256, 0, s>>>(params, grads, momentum, reinterpret_cast<__nv_bfloat16*>(shadow_bf16),
+                                          n4, lr, mu, grad_scale, first_step);
+  else
+    sgd_kernel<false><<<grid, 256, 0, s>>>(params, grads, momentum, reinterpret_cast<__nv_bfloat16*>(shadow_bf16),
+                                           n4, lr, mu, grad_scale, first_step);
+  B200DP_CUDA_OK(cudaGetLastError());
+  return B200DP_OK;
+}
+
+extern "C" int b200dp_cast_f32_bf16(const float* src, void* dst, long long n, void* stream) {
+  B200DP_REQUIRE(src && dst, "cast: null pointer");
+  B200DP_REQUIRE(((uintptr_t)src & 15) == 0 && ((uintptr_t)dst & 7) == 0, "cast: misaligned buffers");
+  cast_kernel<<<ew_grid(n / 4 + 1), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      src, reinterpret_cast<__nv_bfloat16*>(dst), n);
+  B200DP_CUDA_OK(cudaGetLastError());
+  return B200DP_OK;
+}

@@ -58,6 +58,134 @@ typedef struct b200dp_gemm_args {
 
 int b200dp_gemm_bf16(const b200dp_gemm_args* args, void* stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * Whole-network SIMT kernel for MLPs too small for tensor cores (the reference's own 2-3-1 net,
+ * ref.py:41-45): forward + MSE + backward + batch reduction of the gradients in one launch
+ * (everything ref.py:170-176 does).  fp32.  `flat_numel` floats of `params` / `grads` use the
+ * offsets below (weights row-major [out,in]).  scratch: b200dp_tiny_mlp_scratch_bytes(); its first
+ * 4 bytes (a ticket counter) must be zero before the first use and are left zero by every launch.
+ */
+typedef struct b200dp_mlp_desc {
+  int num_layers;
+  int sizes[B200DP_MAX_LAYERS + 1];
+  long long w_off[B200DP_MAX_LAYERS];
+  long long b_off[B200DP_MAX_LAYERS];
+  long long flat_numel;
+} b200dp_mlp_desc;
+
+long long b200dp_tiny_mlp_scratch_bytes(const b200dp_mlp_desc* m, int rows);
+int b200dp_tiny_mlp_fwd_bwd(const b200dp_mlp_desc* m, const float* params, const float* x, const float* y,
+                            int rows, float* grads, float* loss, void* scratch, long long scratch_bytes,
+                            void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Fused MSE loss + gradient (nn.MSELoss() + MseLossBackward, ref.py:94,173,176):
+ *   *loss = mean((pred-target)^2),  dy = 2 (pred-target) / numel.
+ * Deterministic two-stage reduction through `scratch` (b200dp_mse_scratch_bytes(numel) bytes; the
+ * first 4 bytes are a ticket counter that must start at zero and is left at zero).
+ */
+long long b200dp_mse_scratch_bytes(long long numel);
+int b200dp_mse_loss_grad(const void* pred, int pred_bf16, const float* target, long long numel, void* dy,
+                         int dy_bf16, float* loss, void* scratch, long long scratch_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Regression head (last Linear with 1..4 outputs, ref.py:44): GEMV + bias + MSE + dY in one kernel,
+ * and its backward in one pass over H:  dH = (dY W) * [H > 0] (bf16; pass NULL for the first layer),
+ * dW = dY^T H, db = sum dY (fp32 or bf16, fixed-order reduction through scratch).
+ * scratch: b200dp_head_scratch_bytes(rows, K, nout); first 4 bytes zero before first use.
+ */
+long long b200dp_head_scratch_bytes(int rows, int K, int nout);
+int b200dp_head_fwd_mse(const void* H, long long ldh, const void* W, const float* bias, const float* target,
+                        int rows, int K, int nout, float* yhat, float* dy, float* loss, void* scratch,
+                        long long scratch_bytes, void* stream);
+int b200dp_head_bwd(const float* dy, const void* W, const void* H, long long ldh, int rows, int K, int nout,
+                    void* dH, long long lddh, void* dW, void* db, int grads_bf16, void* scratch,
+                    long long scratch_bytes, void* stream);
+
+/* Bias gradient of a GEMM layer: out[n] = sum_rows A[r,n]  (the `sum` of AddmmBackward0, ref.py:176). */
+long long b200dp_colsum_scratch_bytes(int rows, int n);
+int b200dp_colsum_bf16(const void* A, long long lda, int rows, int n, void* out, int out_bf16, void* scratch,
+                       long long scratch_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Local optimizer step, torch.optim.SGD(momentum) semantics (ref.py:91,211):
+ *   g = grads*grad_scale;  buf = first_step ? g : mu*buf + g;  p -= lr*buf;  shadow = bf16(p).
+ */
+int b200dp_sgd_momentum(float* params, const void* grads, int grads_bf16, float* momentum, void* shadow_bf16,
+                        long long n, float lr, float mu, float grad_scale, int first_step, void* stream);
+int b200dp_cast_f32_bf16(const float* src, void* dst, long long n, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Fused all-reduce + weighting + SGD-momentum over NVLink peer memory - the reference's
+ * gather / root average / send / optimizer.step sequence (ref.py:185-211) as ONE kernel per bucket.
+ *   g = (sum_r weights[r]*grads_r) / div  (rank order);  buf = first ? g : mu*buf+g;  p -= lr*buf
+ * mode 0 one-shot (every rank reduces everything), 1 two-shot (rank r owns slice r and pushes the
+ * updated parameters to all peers), 2 NVLS (multimem.ld_reduce / multimem.st; needs mc_* addresses).
+ * Pointer tables hold every rank's buffer as mapped into THIS process (index `rank` = own buffer).
+ * `flags[r]`: rank r's signal pad, B200DP_SYNC_MAX_BLOCKS*B200DP_MAX_RANKS u32, zero-initialised
+ * once.  `epochs`: local, B200DP_SYNC_MAX_BLOCKS u32, zero-initialised once.  `error_flag`: local
+ * u32, set to 1+peer when a peer does not arrive within timeout_ms.
+ * All ranks must issue the same sequence of calls with the same n / mode / max_blocks.
+ */
+#define B200DP_SYNC_MAX_BLOCKS 64
+
+typedef struct b200dp_sync_args {
+  int rank, world;
+  const void* grads[B200DP_MAX_RANKS];   /* fp32 or bf16 */
+  float* params[B200DP_MAX_RANKS];       /* fp32 master */
+  void* shadow[B200DP_MAX_RANKS];        /* bf16 shadow weights, or all NULL */
+  unsigned int* flags[B200DP_MAX_RANKS];
+  float* momentum;                       /* local */
+  unsigned int* epochs;                  /* local */
+  unsigned int* error_flag;              /* local */
+  float weights[B200DP_MAX_RANKS];
+  float div;
+  float lr, mu;
+  int first_step;
+  int grads_bf16;
+  long long offset;                      /* first element of the bucket inside the flat buffers */
+  long long n;                           /* bucket length in elements (multiple of 8) */
+  int mode;
+  int push_master;                       /* modes 1/2: also write fp32 params into the peers */
+  int max_blocks;                        /* 0 = default (32); SM budget of the comm kernel */
+  int timeout_ms;                        /* 0 = wait forever */
+  const void* mc_grads;                  /* NVLS multicast addresses (mode 2) */
+  void* mc_shadow;
+  float* mc_params;
+} b200dp_sync_args;
+
+int b200dp_allreduce_sgd(const b200dp_sync_args* args, void* stream);
+/* One-GPU emulation of a whole world in a single cooperative launch (tests; single-GPU boxes). */
+long long b200dp_sync_args_device_bytes(void);
+int b200dp_allreduce_sgd_emulated(const b200dp_sync_args* per_rank, int world, void* device_args, void* stream);
+/* Cross-GPU barrier on the stream (blocking semantics of the MPI calls at ref.py:185,203). */
+int b200dp_peer_barrier(const b200dp_sync_args* args, void* stream);
+/* Every rank copies `bytes` from args->params[root] into args->params[rank] (ref.py:87-88). */
+int b200dp_broadcast(const b200dp_sync_args* args, int root, long long bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Symmetric (peer-mapped) memory.  Replaces MPI.COMM_WORLD as the transport (ref.py:61-63): each
+ * rank allocates, exports a handle, peers import it and get a pointer valid in their own address
+ * space.  Two flavours:
+ *   ipc : cudaMalloc + cudaIpcMemHandle (64 opaque bytes, exchanged by the host-side store).
+ *   vmm : cuMemCreate + POSIX fd; peers duplicate the fd with pidfd_getfd().  Needed for NVLS:
+ *         b200dp_mc_* bind the same allocations into a multicast object.
+ */
+int b200dp_ipc_alloc(long long bytes, void** ptr, unsigned char* handle64);
+int b200dp_ipc_open(const unsigned char* handle64, void** ptr);
+int b200dp_ipc_close(void* ptr);
+int b200dp_ipc_free(void* ptr);
+
+int b200dp_vmm_supported(int* fd_export, int* multicast);
+int b200dp_vmm_alloc(long long bytes, void** ptr, int* fd, long long* padded_bytes);
+int b200dp_vmm_import(int owner_pid, int owner_fd, long long padded_bytes, void** ptr);
+int b200dp_vmm_free(void* ptr, long long padded_bytes);
+int b200dp_mc_create(int world, long long padded_bytes, int* fd, unsigned long long* mc_handle);
+int b200dp_mc_import(int owner_pid, int owner_fd, unsigned long long* mc_handle);
+int b200dp_mc_add_device(unsigned long long mc_handle);
+int b200dp_mc_bind(unsigned long long mc_handle, void* local_ptr, long long padded_bytes, void** mc_ptr);
+int b200dp_mc_release(unsigned long long mc_handle, void* mc_ptr, long long padded_bytes);
+
 #ifdef __cplusplus
 }
 #endif

@@ -119,6 +119,9 @@ class Trainer:
     def step(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
         """One synchronous data-parallel step (ref.py:164-211).  Returns the local pre-update loss
         as a 0-dim device tensor (no host sync)."""
+        begin = getattr(self.sync, "begin_step", None)
+        if begin is not None:                      # fused sync: buckets are queued from inside backward
+            begin(self.cfg.lr, self.cfg.momentum)
         with self.timer.phase("fwd_bwd"):
             loss = self.compute.loss_and_grads(x, y)
         with self.timer.phase("sync_update"):
@@ -141,6 +144,9 @@ class Trainer:
                 loss_val = float("nan")
             else:
                 loss_val = float(loss.item())                                   # ref.py:224
+                check = getattr(self.sync, "check_errors", None)
+                if check is not None:
+                    check()                                                     # watchdog
             emit(loss_line(self.rank, loss_val), cfg.quiet)
             rec = {"epoch": epoch, "rank": self.rank, "loss": loss_val,
                    "epoch_s": time.perf_counter() - t0}
@@ -162,6 +168,71 @@ class Trainer:
         if cfg.checkpoint:
             self.save_checkpoint(cfg.checkpoint, cfg.nepochs)
         return self.history
+
+    # ------------------------------------------------------------------ host-fed training
+    def fit_host_batches(self, batches, steps: int, on_loss=None) -> List[float]:
+        """Trains ``steps`` steps on batches that live in (pinned) HOST memory - the end-to-end path
+        a user with a real dataset takes.  ``batches`` yields ``(x_host, y_host)``; every step's
+        inputs cross PCIe in that step (prefetched one step ahead on a copy stream into a double
+        buffer) and every step's loss is copied back to pinned host memory and read by the host
+        (one step behind the GPU, so the queue never drains).  Returns the per-step losses."""
+        if self.device.type != "cuda":
+            out = []
+            for _, (xh, yh) in zip(range(steps), batches):
+                xb, yb = self.compute.prepare_batch(xh.to(self.device), yh.to(self.device))
+                out.append(float(self.step(xb, yb).item()))
+            return out
+        dev = self.device
+        main = torch.cuda.current_stream()
+        copy_stream = torch.cuda.Stream(device=dev)
+        it = iter(batches)
+        slots = [None, None]
+        ready = [torch.cuda.Event(), torch.cuda.Event()]
+        consumed = [torch.cuda.Event(), torch.cuda.Event()]
+        loss_host = torch.zeros(max(steps, 1), dtype=torch.float32).pin_memory()
+        loss_evt = [torch.cuda.Event() for _ in range(max(steps, 1))]
+        self.h2d_bytes_per_step = 0
+        self.d2h_bytes_per_step = 4
+
+        def stage(i):
+            xh, yh = next(it)
+            k = i & 1
+            with torch.cuda.stream(copy_stream):
+                copy_stream.wait_event(consumed[k])               # the step that used this slot is done
+                if slots[k] is None or slots[k][0].shape != xh.shape or slots[k][0].dtype != xh.dtype:
+                    slots[k] = (torch.empty(xh.shape, dtype=xh.dtype, device=dev),
+                                torch.empty(yh.shape, dtype=yh.dtype, device=dev))
+                slots[k][0].copy_(xh, non_blocking=True)
+                slots[k][1].copy_(yh, non_blocking=True)
+                ready[k].record(copy_stream)
+            self.h2d_bytes_per_step = xh.numel() * xh.element_size() + yh.numel() * yh.element_size()
+
+        losses: List[float] = []
+        if steps > 0:
+            stage(0)
+        for i in range(steps):
+            k = i & 1
+            if i + 1 < steps:
+                stage(i + 1)
+            main.wait_event(ready[k])
+            xd, yd = slots[k]
+            xb, yb = (xd, yd) if (xd.dtype == self.x.dtype and yd.dtype == self.y.dtype) \
+                else self.compute.prepare_batch(xd, yd)
+            loss = self.step(xb, yb)
+            consumed[k].record(main)
+            loss_host[i:i + 1].copy_(loss.reshape(1), non_blocking=True)
+            loss_evt[i].record(main)
+            if i >= 1:                                            # read step i-1's loss on the host
+                loss_evt[i - 1].synchronize()
+                losses.append(float(loss_host[i - 1]))
+                if on_loss is not None:
+                    on_loss(i - 1, losses[-1])
+        if steps > 0:
+            loss_evt[steps - 1].synchronize()
+            losses.append(float(loss_host[steps - 1]))
+            if on_loss is not None:
+                on_loss(steps - 1, losses[-1])
+        return losses
 
     # ------------------------------------------------------------------ extras
     def _global_loss(self, local: float) -> float:

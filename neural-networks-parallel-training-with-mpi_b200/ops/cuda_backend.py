@@ -1,0 +1,473 @@
+"""CUDA backend of the trainer: wires the sm_100a kernels of libb200dp into the step schedule.
+
+Per step (ref.py:164-211) on one GPU:
+
+  tiny nets (fp32, e.g. the reference's 2-3-1)       wide / deep nets (bf16)
+  -------------------------------------------       ----------------------------------------------
+  1 launch: tiny_mlp fwd+MSE+bwd -> grad bucket      fwd: tcgen05 GEMM per hidden layer (bias+ReLU
+  1 launch: fused all-reduce+SGD (or local SGD)           fused), head GEMV fused with MSE + dY
+                                                     bwd: per layer wgrad GEMM (writes bf16 grads
+                                                          straight into the bucket), column-sum for
+                                                          db, dgrad GEMM with fused ReLU mask
+                                                     sync: as soon as a layer's bucket is complete
+                                                          its fused all-reduce+SGD kernel is queued
+                                                          on a second stream and overlaps the rest
+                                                          of backward.
+
+No PyTorch op runs inside the step; torch only owns memory and streams.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Callable, List, Optional, Tuple
+
+import torch
+
+from ..models.mlp import FlatMLP, MLPSpec
+from ..parallel.grad_sync import GradSync, weights_and_divisor
+from ..parallel.symm_mem import SymmetricBuffer
+from . import _lib, allreduce_sgd as ar, gemm, kernels as K
+
+TINY_MAX_DIM = 64
+TINY_MAX_PARAMS = 16384
+
+
+def _align(n: int, a: int = 256) -> int:
+    return (n + a - 1) // a * a
+
+
+def is_tiny(spec: MLPSpec) -> bool:
+    return max(spec.sizes) <= TINY_MAX_DIM and spec.flat_numel <= TINY_MAX_PARAMS
+
+
+# =============================================================================== compute: tiny
+class TinyCompute:
+    """Whole net in one SIMT launch (``csrc/tiny_mlp.cu``)."""
+    name = "cuda-tiny"
+
+    def __init__(self, flat: FlatMLP, max_rows: int):
+        self.flat = flat
+        self.desc = K.mlp_desc(flat.spec)
+        dev = flat.device
+        self.scratch = K.scratch(K.tiny_mlp_scratch_bytes(flat.spec, max(max_rows, 1)), dev)
+        self.loss = torch.zeros((), dtype=torch.float32, device=dev)
+        self.bucket_hook: Optional[Callable[[int], None]] = None
+
+    def prepare_batch(self, x, y):
+        return x.to(torch.float32).contiguous(), y.to(torch.float32).contiguous()
+
+    def loss_and_grads(self, x, y) -> torch.Tensor:
+        if x.shape[0] == 0:
+            self.flat.grads.zero_()
+            self.loss.fill_(float("nan"))
+        else:
+            K.tiny_mlp_fwd_bwd(self.desc, self.flat.params, x, y, self.flat.grads, self.loss, self.scratch)
+        if self.bucket_hook is not None:
+            for l in reversed(range(self.flat.spec.num_layers)):
+                self.bucket_hook(l)
+        return self.loss
+
+    def predict(self, x):
+        from . import reference as ref_ops
+        return ref_ops.mlp_forward(self.flat, x.to(torch.float32)).to(torch.float32)
+
+
+# =============================================================================== compute: gemm
+class GemmCompute:
+    """bf16 tensor-core path: tcgen05 GEMMs + fused head/MSE kernels."""
+    name = "cuda-tcgen05"
+
+    def __init__(self, flat: FlatMLP, max_rows: int):
+        spec = flat.spec
+        if flat.shadow is None:
+            raise ValueError("the tensor-core path trains in bf16 (use --dtype bf16)")
+        for s in spec.sizes[:-1]:
+            if s % 8:
+                raise ValueError(f"tensor-core path needs feature / hidden sizes that are multiples of 8 (got {s})")
+        self.nout = spec.sizes[-1]
+        if self.nout > 4 and self.nout % 8:
+            raise ValueError("n_outputs must be <= 4 (fused GEMV head) or a multiple of 8 (GEMM head)")
+        self.flat, self.spec, self.L = flat, spec, spec.num_layers
+        dev = flat.device
+        R = max(max_rows, 1)
+        self.max_rows = R
+        bf = torch.bfloat16
+        # activations a[l] = input of layer l (a[0] is the batch itself); d[l] = dLoss/da[l]
+        self.acts: List[Optional[torch.Tensor]] = [None] + [
+            torch.empty(R, spec.sizes[l], dtype=bf, device=dev) for l in range(1, self.L)]
+        hid = max(spec.sizes[1:self.L], default=8)
+        self.dbuf = [torch.empty(R * hid, dtype=bf, device=dev) for _ in range(2)]
+        self.loss = torch.zeros((), dtype=torch.float32, device=dev)
+        self.head_is_gemv = self.nout <= 4
+        if self.head_is_gemv:
+            self.yhat = torch.empty(R, self.nout, dtype=torch.float32, device=dev)
+            self.dy32 = torch.empty(R, self.nout, dtype=torch.float32, device=dev)
+            self.head_scratch = K.scratch(K.head_scratch_bytes(R, spec.sizes[self.L - 1], self.nout), dev)
+        else:
+            self.yhat = torch.empty(R, self.nout, dtype=bf, device=dev)
+            self.dyb = torch.empty(R, self.nout, dtype=bf, device=dev)
+            self.mse_scratch = K.scratch(K.mse_scratch_bytes(R * self.nout), dev)
+        widest = max(spec.sizes[1:])
+        self.colsum_scratch = K.scratch(K.colsum_scratch_bytes(R, _align(widest, 8)), dev)
+        self.bucket_hook: Optional[Callable[[int], None]] = None
+        self.gemm_max_ctas = 0
+
+    def prepare_batch(self, x, y):
+        xb = torch.empty(x.shape, dtype=torch.bfloat16, device=x.device)
+        if x.numel():
+            if x.dtype == torch.bfloat16:
+                xb.copy_(x)
+            else:
+                K.cast_f32_bf16(x.to(torch.float32).contiguous(), xb)
+        return xb, y.to(torch.float32).contiguous()
+
+    # ---- views ----
+    def _w(self, l):
+        return self.flat.weight(l, self.flat.shadow)
+
+    def _gw(self, l):
+        return self.flat.weight(l, self.flat.grads)
+
+    def _gb(self, l):
+        return self.flat.bias(l, self.flat.grads)
+
+    def _d(self, idx, rows, width):
+        return self.dbuf[idx & 1][:rows * width].view(rows, width)
+
+    def forward_hidden(self, x) -> torch.Tensor:
+        rows = x.shape[0]
+        h = x
+        for l in range(self.L - 1):
+            out = self.acts[l + 1][:rows]
+            gemm.linear_fwd(h, self._w(l), self.flat.bias(l), relu=True, out=out, max_ctas=self.gemm_max_ctas)
+            h = out
+        return h
+
+    def loss_and_grads(self, x, y) -> torch.Tensor:
+        rows = x.shape[0]
+        if rows == 0:
+            self.flat.grads.zero_()
+            self.loss.fill_(float("nan"))
+            if self.bucket_hook is not None:
+                for l in reversed(range(self.L)):
+                    self.bucket_hook(l)
+            return self.loss
+        L, flat = self.L, self.flat
+        h = self.forward_hidden(x)
+        last = L - 1
+        # ---- head forward + loss + dY, head backward ----
+        if self.head_is_gemv:
+            yhat, dy = self.yhat[:rows], self.dy32[:rows]
+            K.head_fwd_mse(h, self._w(last), flat.bias(last), y, yhat, dy, self.loss, self.head_scratch)
+            dnext = self._d(last, rows, self.spec.sizes[last]) if last > 0 else None
+            K.head_bwd(dy, self._w(last), h, dnext, self._gw(last), self._gb(last), self.head_scratch)
+        else:
+            yhat, dy = self.yhat[:rows], self.dyb[:rows]
+            gemm.linear_fwd(h, self._w(last), flat.bias(last), relu=False, out=yhat, max_ctas=self.gemm_max_ctas)
+            K.mse_loss_grad(yhat, y, dy, self.loss, self.mse_scratch)
+            gemm.linear_wgrad(dy, h, out=self._gw(last), max_ctas=self.gemm_max_ctas)
+            K.colsum(dy, self._gb(last), self.colsum_scratch)
+            dnext = None
+            if last > 0:
+                dnext = self._d(last, rows, self.spec.sizes[last])
+                gemm.linear_dgrad(dy, self._w(last), h, out=dnext, max_ctas=self.gemm_max_ctas)
+        if self.bucket_hook is not None:
+            self.bucket_hook(last)
+        # ---- hidden layers, top down ----
+        for l in range(L - 2, -1, -1):
+            dy_l = dnext                                   # dLoss/d(pre-activation of layer l), [rows, sizes[l+1]]
+            a_in = x if l == 0 else self.acts[l][:rows]
+            gemm.linear_wgrad(dy_l, a_in, out=self._gw(l), max_ctas=self.gemm_max_ctas)
+            K.colsum(dy_l, self._gb(l), self.colsum_scratch)
+            if l > 0:
+                dnext = self._d(l, rows, self.spec.sizes[l])
+                gemm.linear_dgrad(dy_l, self._w(l), a_in, out=dnext, max_ctas=self.gemm_max_ctas)
+            if self.bucket_hook is not None:
+                self.bucket_hook(l)
+        return self.loss
+
+    @torch.no_grad()
+    def predict(self, x) -> torch.Tensor:
+        xb, _ = self.prepare_batch(x, torch.zeros(x.shape[0], self.nout, device=x.device))
+        rows = xb.shape[0]
+        if rows > self.max_rows:
+            return torch.cat([self.predict(x[i:i + self.max_rows]) for i in range(0, rows, self.max_rows)])
+        h = self.forward_hidden(xb)
+        last = self.L - 1
+        w, b = self._w(last), self.flat.bias(last)
+        return h.float() @ w.float().t() + b        # evaluation only, off the training path
+
+
+# =============================================================================== sync strategies
+@dataclass
+class Bucket:
+    lo_layer: int
+    hi_layer: int
+    start: int
+    stop: int
+
+
+def make_buckets(spec: MLPSpec, bucket_mb: float, elem_bytes: int) -> List[Bucket]:
+    """Per-layer buckets (bucket_mb == 0) or consecutive layers merged up to ``bucket_mb``; built top
+    layer first, the order backward completes them."""
+    out: List[Bucket] = []
+    limit = int(bucket_mb * (1 << 20))
+    cur: Optional[Bucket] = None
+    for l in reversed(range(spec.num_layers)):
+        s, e = spec.layer_span(l)
+        if cur is not None and limit > 0 and (cur.stop - s) * elem_bytes <= limit:
+            cur.lo_layer, cur.start = l, s
+        else:
+            if cur is not None:
+                out.append(cur)
+            cur = Bucket(l, l, s, e)
+    if cur is not None:
+        out.append(cur)
+    return out
+
+
+class CudaLocalSync(GradSync):
+    """World of one: the fused SGD kernel over the flat buffers."""
+    name = "cuda_local"
+
+    def sync_and_step(self, flat, lr, mu):
+        K.sgd_momentum(flat.params, flat.grads, flat.momentum, flat.shadow, lr, mu, first_step=False,
+                       grad_scale=1.0)
+        flat.step_count += 1
+
+
+class NcclAllReduceSync(GradSync):
+    """Library baseline: ``torch.distributed.all_reduce`` (NCCL) on the gradient buffer, then the
+    local SGD kernel.  Measured against, not shipped as the product path."""
+    name = "allreduce"
+
+    def sync_and_step(self, flat, lr, mu):
+        import torch.distributed as dist
+        w = self.weights[self.comm.rank]
+        if w != 1.0:
+            flat.grads.mul_(w)
+        dist.all_reduce(flat.grads, op=dist.ReduceOp.SUM)
+        K.sgd_momentum(flat.params, flat.grads, flat.momentum, flat.shadow, lr, mu, first_step=False,
+                       grad_scale=1.0 / self.divisor)
+        flat.step_count += 1
+
+
+class CudaGatherRootSync(GradSync):
+    """The reference's protocol (gather -> root average -> send, ref.py:185-203) with device
+    tensors staged through the host communicator; baseline only."""
+    name = "gather_root"
+
+    def sync_and_step(self, flat, lr, mu):
+        from . import reference as ref_ops
+        comm = self.comm
+        grad_list = comm.gather(flat.grads.detach().to("cpu"), root=0)
+        if comm.rank == 0:
+            avg = ref_ops.reduce_grads(grad_list, self.weights, self.divisor)
+            for k in range(1, comm.size):
+                comm.send(avg, k)
+        else:
+            avg = comm.recv(0)
+        g = avg.to(flat.params.device, torch.float32)
+        K.sgd_momentum(flat.params, g, flat.momentum, flat.shadow, lr, mu, first_step=False)
+        flat.step_count += 1
+
+
+class FusedSync(GradSync):
+    """The product path: one fused all-reduce + SGD kernel per bucket over NVLink peer memory,
+    queued on a side stream as soon as backward has produced the bucket."""
+
+    def __init__(self, comm, weights, divisor, mode: str, flat: FlatMLP, symm: "SymmLayout",
+                 buckets: List[Bucket], overlap: bool, max_blocks: int, timeout_ms: int):
+        super().__init__(comm, weights, divisor)
+        self.name = mode
+        self.flat, self.symm, self.buckets, self.overlap = flat, symm, buckets, overlap
+        dev = flat.device
+        self.epochs = torch.zeros(ar.SYNC_MAX_BLOCKS, dtype=torch.int32, device=dev)
+        self.error_flag = torch.zeros(1, dtype=torch.int32, device=dev)
+        bf16 = flat.grads.dtype == torch.bfloat16
+        m = ar.MODES[mode]
+        # bf16 training ships only the bf16 shadow to the peers; the fp32 master of a slice lives
+        # on its owner (gathered on demand).  fp32 training ships the fp32 values themselves.
+        self.push_master = flat.shadow is None
+        self.args = ar.make_args(
+            comm.rank, comm.size, symm.ptrs("grads"), symm.ptrs("params"),
+            symm.ptrs("shadow") if flat.shadow is not None else None, symm.ptrs("flags"),
+            flat.momentum.data_ptr(), self.epochs.data_ptr(), self.error_flag.data_ptr(), weights, divisor,
+            bf16, m, self.push_master, max_blocks, timeout_ms,
+            symm.mc("grads"), symm.mc("shadow") if flat.shadow is not None else None, symm.mc("params"))
+        self.sharded_master = (m != 0) and not self.push_master
+        self.comm_stream = torch.cuda.Stream(device=dev) if overlap else None
+        self._ready = torch.cuda.Event()
+        self._done = torch.cuda.Event()
+        self._launched = set()
+        self._lr = self._mu = None
+        self._by_lo = {b.lo_layer: i for i, b in enumerate(buckets)}
+
+    # called by the compute backend right after layer `l`'s backward has been queued
+    def bucket_ready(self, l: int) -> None:
+        i = self._by_lo.get(l)
+        if i is None or self._lr is None:
+            return
+        self._launch(i)
+
+    def _launch(self, i: int) -> None:
+        if i in self._launched:
+            return
+        b = self.buckets[i]
+        main = torch.cuda.current_stream()
+        if self.comm_stream is not None:
+            self._ready.record(main)
+            self.comm_stream.wait_event(self._ready)
+            ar.launch(self.args, b.start, b.stop - b.start, self._lr, self._mu, False, stream=self.comm_stream)
+        else:
+            ar.launch(self.args, b.start, b.stop - b.start, self._lr, self._mu, False, stream=main)
+        self._launched.add(i)
+
+    def begin_step(self, lr: float, mu: float) -> None:
+        self._lr, self._mu = lr, mu
+        self._launched.clear()
+
+    def sync_and_step(self, flat, lr, mu):
+        if self._lr is None:
+            self.begin_step(lr, mu)
+        for i in range(len(self.buckets)):
+            self._launch(i)
+        if self.comm_stream is not None:
+            self._done.record(self.comm_stream)
+            torch.cuda.current_stream().wait_event(self._done)
+        self._lr = None
+        flat.step_count += 1
+
+    def check_errors(self) -> None:
+        v = int(self.error_flag.item())
+        if v:
+            raise RuntimeError(f"fused gradient sync timed out waiting for rank {v - 1} "
+                               "(peer dead or launch sequences diverged)")
+
+
+class SymmLayout:
+    """Carves one SymmetricBuffer into the regions the fused kernels need."""
+
+    def __init__(self, comm, device, numel: int, grads_bf16: bool, with_shadow: bool, multicast: bool):
+        self.regions = {}
+        off = 0
+        for name, nbytes in (("flags", ar.FLAG_BYTES), ("params", numel * 4),
+                             ("grads", numel * (2 if grads_bf16 else 4)),
+                             ("shadow", numel * 2 if with_shadow else 0)):
+            self.regions[name] = (off, nbytes)
+            off = _align(off + nbytes, 1024)
+        self.buf = SymmetricBuffer(comm, off, device, flavour="auto", multicast=multicast)
+
+    def ptrs(self, name: str) -> List[int]:
+        off, _ = self.regions[name]
+        return [p + off for p in self.buf.ptrs]
+
+    def mc(self, name: str) -> Optional[int]:
+        if self.buf.mc_ptr is None:
+            return None
+        return self.buf.mc_ptr + self.regions[name][0]
+
+    def tensor(self, name: str, dtype) -> torch.Tensor:
+        off, nbytes = self.regions[name]
+        item = torch.empty((), dtype=dtype).element_size()
+        return self.buf.tensor(dtype, nbytes // item, off)
+
+
+# =============================================================================== runtime
+class CudaRuntime:
+    def __init__(self, trainer):
+        cfg, comm, dev = trainer.cfg, trainer.comm, trainer.device
+        _lib.lib()                                     # fail loudly if the native library is missing
+        spec: MLPSpec = trainer.spec
+        self.comm, self.cfg = comm, cfg
+        tiny = is_tiny(spec) and cfg.dtype == "fp32"
+        if not tiny and cfg.dtype != "bf16":
+            raise ValueError("models beyond the fused SIMT kernel's size train on the tensor-core path: "
+                             "pass --dtype bf16")
+        sync_name = cfg.sync
+        if sync_name == "auto":
+            sync_name = "fused_twoshot" if comm.size > 1 else "local"
+            if comm.size > 1 and spec.flat_numel * 4 <= 256 * 1024:
+                sync_name = "fused_oneshot"
+        fused = comm.size > 1 and sync_name.startswith("fused")
+        weights, divisor = weights_and_divisor(trainer.counts, cfg.grad_weighting)
+        self.symm: Optional[SymmLayout] = None
+        grads_bf16 = cfg.dtype == "bf16"
+        if fused:
+            self.symm = SymmLayout(comm, dev, spec.flat_numel, grads_bf16, cfg.dtype == "bf16",
+                                   multicast=(sync_name == "fused_nvls"))
+            if sync_name == "fused_nvls" and self.symm.buf.mc_ptr is None:
+                if comm.rank == 0:
+                    print("b200dp: NVLS multicast is not available on this box - using fused_twoshot")
+                sync_name = "fused_twoshot"
+            self.flat = FlatMLP(spec, dev, cfg.dtype,
+                                grads=self.symm.tensor("grads", torch.bfloat16 if grads_bf16 else torch.float32),
+                                shadow=self.symm.tensor("shadow", torch.bfloat16) if cfg.dtype == "bf16" else None,
+                                params=self.symm.tensor("params", torch.float32))
+        else:
+            self.flat = FlatMLP(spec, dev, cfg.dtype)
+        max_rows = trainer.shard.rows
+        self.compute = TinyCompute(self.flat, max_rows) if tiny else GemmCompute(self.flat, max_rows)
+        self.buckets = make_buckets(spec, cfg.bucket_mb, 2 if grads_bf16 else 4)
+        if tiny:
+            self.buckets = [Bucket(0, spec.num_layers - 1, 0, spec.flat_numel)]
+        self.device_broadcast = None
+        if comm.size == 1:
+            self.sync: GradSync = CudaLocalSync(comm, weights, divisor)
+        elif fused:
+            self.sync = FusedSync(comm, weights, divisor, sync_name, self.flat, self.symm, self.buckets,
+                                  overlap=cfg.overlap and not tiny, max_blocks=0, timeout_ms=cfg.watchdog_ms)
+            self.compute.bucket_hook = self.sync.bucket_ready
+            self.device_broadcast = self._device_broadcast
+        elif sync_name == "allreduce":
+            self.sync = NcclAllReduceSync(comm, weights, divisor)
+        elif sync_name == "gather_root":
+            self.sync = CudaGatherRootSync(comm, weights, divisor)
+        else:
+            raise ValueError(f"unknown sync mode {sync_name!r}")
+        self.sync_name = sync_name
+
+    def _device_broadcast(self, params: torch.Tensor) -> None:
+        """K9: every rank pulls rank 0's parameters from peer memory (ref.py:87-88)."""
+        torch.cuda.synchronize()
+        self.comm.barrier()
+        ar.broadcast(self.sync.args, 0, params.numel() * 4)
+        torch.cuda.synchronize()
+        self.comm.barrier()
+
+    def gather_optimizer_state(self) -> None:
+        """bf16 two-shot / NVLS keep the fp32 master and the momentum of a slice only on its owner
+        (ZeRO-1 style).  Before a checkpoint the slices are collected on every rank."""
+        sync = self.sync
+        if not isinstance(sync, FusedSync):
+            return
+        import torch.distributed as dist
+        torch.cuda.synchronize()
+        world, rank = self.comm.size, self.comm.rank
+        vn = 8 if self.flat.grads.dtype == torch.bfloat16 else 4
+        if ar.MODES[sync.name] == 0:
+            return
+        for b in self.buckets:
+            units = (b.stop - b.start) // vn
+            for r in range(world):
+                lo = b.start + units * r // world * vn
+                hi = b.start + units * (r + 1) // world * vn
+                if hi > lo:
+                    dist.broadcast(self.flat.momentum[lo:hi], src=r)
+                    if sync.sharded_master:
+                        dist.broadcast(self.flat.params[lo:hi], src=r)
+        torch.cuda.synchronize()
+
+    def close(self) -> None:
+        if isinstance(self.sync, FusedSync):
+            try:
+                self.sync.check_errors()
+            finally:
+                pass
+        if self.symm is not None:
+            self.symm.buf.close()
+            self.symm = None
+
+
+def build_cuda_runtime(trainer) -> CudaRuntime:
+    return CudaRuntime(trainer)
