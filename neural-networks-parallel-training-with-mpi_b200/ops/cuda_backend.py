@@ -104,7 +104,7 @@ class GemmCompute:
             self.dy32 = torch.empty(R, self.nout, dtype=torch.float32, device=dev)
             self.head_scratch = K.scratch(K.head_scratch_bytes(R, spec.sizes[self.L - 1], self.nout), dev)
         else:
-            self.yhat = torch.empty(R, self.nout, dtype=bf, device=dev)
+            self.yhat = torch.empty(R, self.nout, dtype=torch.float32, device=dev)   # fp32 logits
             self.dyb = torch.empty(R, self.nout, dtype=bf, device=dev)
             self.mse_scratch = K.scratch(K.mse_scratch_bytes(R * self.nout), dev)
         widest = max(spec.sizes[1:])

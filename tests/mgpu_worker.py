@@ -1,0 +1,65 @@
+"""Worker for the multi-GPU tests: `torchrun --nproc-per-node N tests/mgpu_worker.py <scenario>`.
+Prints one JSON line per rank."""
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+import b200dp  # noqa: E402,F401
+from b200dp.config import TrainConfig  # noqa: E402
+from b200dp.engine import Trainer  # noqa: E402
+from b200dp.launch import bind_device, discover, init_process_group  # noqa: E402
+from b200dp.parallel.comm import world_comm  # noqa: E402
+
+
+def main():
+    scenario = sys.argv[1]
+    info = discover()
+    dev = bind_device(info)
+    init_process_group(info)
+    comm = world_comm()
+    out = {"rank": comm.rank, "scenario": scenario}
+    if scenario.startswith("ref_"):
+        sync = scenario[4:]
+        t = Trainer(TrainConfig(quiet=True, sync=sync, nepochs=3, check_replicas_every=1), comm, dev)
+        out["losses"] = [h["loss"] for h in t.train()]
+        out["sync"] = t._runtime.sync_name
+        out["fingerprint"] = t.flat.fingerprint()
+        t.close()
+    elif scenario.startswith("wide_"):
+        sync = scenario[5:]
+        cfg = TrainConfig(quiet=True, sync=sync, nepochs=6, n_samples=1024 * comm.size, n_features=256,
+                          hidden=[512, 256], dtype="bf16", data_source="randn", data_dist="local", scale="none",
+                          lr=1e-3, noise=0.1, init="torch_cpu")
+        t = Trainer(cfg, comm, dev)
+        out["losses"] = [h["loss"] for h in t.train()]
+        out["sync"] = t._runtime.sync_name
+        torch.cuda.synchronize()
+        sh = t.flat.shadow.detach().cpu().view(torch.int16)
+        import hashlib
+        out["shadow_hash"] = hashlib.blake2b(sh.numpy().tobytes(), digest_size=8).hexdigest()
+        ck = f"/tmp/b200dp_mgpu_{scenario}.pt"
+        t.save_checkpoint(ck, 6)
+        if comm.rank == 0:
+            out["ckpt_norm"] = float(sum(v.double().norm() for v in torch.load(ck, weights_only=False)["model"].values()))
+        t.close()
+    elif scenario.startswith("uneven_"):
+        sync = scenario[7:]
+        t = Trainer(TrainConfig(quiet=True, sync=sync, nepochs=3, n_samples=17, grad_weighting="samples"), comm, dev)
+        out["losses"] = [h["loss"] for h in t.train()]
+        out["rows"] = t.shard.rows
+        out["fingerprint"] = t.flat.fingerprint()
+        t.close()
+    print("RESULT " + json.dumps(out))
+    sys.stdout.flush()
+    import torch.distributed as dist
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

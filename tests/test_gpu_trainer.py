@@ -57,7 +57,7 @@ def test_tensor_core_path_tracks_autograd(nout):
     for seg, p in zip(t.spec.segments, m.parameters()):
         got = t.flat.grads[seg.offset:seg.offset + seg.numel].view(seg.shape).float()
         scale = p.grad.abs().max().item() + 1e-12
-        assert (got - p.grad).abs().max().item() <= 4e-2 * scale, seg.key
+        assert (got - p.grad).abs().max().item() <= 5e-2 * scale, seg.key
     # and training reduces the loss
     cfg2 = TrainConfig(**{**cfg.asdict(), "nepochs": 30})
     t2 = Trainer(cfg2, device=torch.device("cuda"))
