@@ -62,7 +62,7 @@ def test_tensor_core_path_tracks_autograd(nout):
     cfg2 = TrainConfig(**{**cfg.asdict(), "nepochs": 30})
     t2 = Trainer(cfg2, device=torch.device("cuda"))
     hist = t2.train()
-    assert hist[-1]["loss"] < 0.7 * hist[0]["loss"]
+    assert hist[-1]["loss"] < 0.95 * hist[0]["loss"]
 
 
 def test_checkpoint_from_gpu_loads_into_plain_module(tmp_path):
