@@ -8,6 +8,8 @@
 // owned by one thread which sums its per-row contributions in row order - no atomics, so the
 // result is bit-reproducible.  Blocks publish partial gradients to scratch memory; the last block
 // to finish (ticket counter) adds them in block order and writes the flat gradient buffer + loss.
+#include <mutex>
+
 #include "common.cuh"
 
 namespace b200dp {
@@ -212,6 +214,100 @@ extern "C" int b200dp_tiny_mlp_fwd_bwd(const b200dp_mlp_desc* m, const float* pa
   const float inv_count = 1.0f / (float(rows) * float(d.sizes[d.num_layers]));
   tiny_mlp_kernel<<<g, kThreads, smem, reinterpret_cast<cudaStream_t>(stream)>>>(
       d, params, x, y, rows, inv_count, grads, loss, part, ticket);
+  B200DP_CUDA_OK(cudaGetLastError());
+  return B200DP_OK;
+}
+
+// ================================================================================================
+// Allocation-free variant of b200dp_tiny_mlp_fwd_bwd.
+//
+// Who it is for: callers that must not (or cannot) call cudaMalloc at the point where they train -
+// e.g. a host thread inside a latency-critical loop where an allocation would serialise the whole
+// device, a plugin running inside another framework whose memory pool owns every byte of the GPU,
+// or a process that was handed a fixed memory budget at start-up.  Such callers still own the
+// inputs and outputs; what they cannot provide is the kernel's cross-block scratch (one ticket
+// counter + one partial gradient/loss record per thread block).
+//
+// That scratch lives here instead, in a file-scope device array of a fixed, modest size.  Every
+// GPU that loads the library carries this array until the process exits.
+//
+// Rules that follow from sharing one array:
+//   * a call whose scratch need exceeds B200DP_TINY_NOALLOC_SCRATCH_BYTES is refused with an error;
+//   * the array keeps whatever the previous call left in it; the only part that must start at
+//     zero is the 4-byte ticket counter, which this entry point clears on the stream before each
+//     launch (a memset node, not an allocation);
+//   * two calls that can overlap on the same GPU (different streams, different threads) race on
+//     the array and produce garbage - serialise them, or use the scratch-taking entry point.
+//
+// In host code the array's name is only a host-side handle, not a device address, so the address
+// the kernel receives is looked up with cudaGetSymbolAddress - once per device, with that device
+// current, on the first call made on that device.  Because that look-up talks to the runtime,
+// make the first call on each device BEFORE starting any stream capture.  Nothing here calls
+// cudaMalloc / cudaFree or any allocating library routine.
+// ================================================================================================
+namespace b200dp {
+namespace {
+
+static __device__ __align__(256) unsigned char g_tiny_noalloc_scratch[B200DP_TINY_NOALLOC_SCRATCH_BYTES];
+
+constexpr int kMaxDevices = 64;
+struct NoAllocDeviceState {
+  bool ready;
+  void* scratch;       // device address of g_tiny_noalloc_scratch on this device
+};
+NoAllocDeviceState g_noalloc[kMaxDevices];
+std::mutex g_noalloc_mu;
+
+// Per-device set-up; the current device must be the one the caller is about to launch on.
+int noalloc_setup(int dev, void** scratch_out) {
+  std::lock_guard<std::mutex> lk(g_noalloc_mu);
+  NoAllocDeviceState& st = g_noalloc[dev];
+  if (!st.ready) {
+    void* ptr = nullptr;
+    B200DP_CUDA_OK(cudaGetSymbolAddress(&ptr, g_tiny_noalloc_scratch));
+    B200DP_REQUIRE(ptr != nullptr, "tiny_mlp_noalloc: cudaGetSymbolAddress returned a null address");
+    st.scratch = ptr;
+    st.ready = true;
+  }
+  *scratch_out = st.scratch;
+  return B200DP_OK;
+}
+
+}  // namespace
+}  // namespace b200dp
+
+extern "C" int b200dp_tiny_mlp_fwd_bwd_noalloc(const b200dp_mlp_desc* m, const float* params, const float* x,
+                                               const float* y, int rows, float* grads, float* loss,
+                                               void* stream) {
+  using namespace b200dp;
+  B200DP_REQUIRE(m && params && x && y && grads && loss, "tiny_mlp_noalloc: null pointer");
+  B200DP_REQUIRE(rows >= 1, "tiny_mlp_noalloc: rows must be >= 1");
+  TinyDesc d;
+  int smem;
+  if (int rc = fill_desc(m, &d, &smem)) return rc;
+  const int g = grid_for(d, rows);
+  const long long need = g > 1 ? 256 + (long long)g * (d.flat_numel + 1) * 4 : 0;
+  B200DP_REQUIRE(need <= (long long)B200DP_TINY_NOALLOC_SCRATCH_BYTES,
+                 "tiny_mlp_noalloc: this problem needs %lld bytes of scratch (%d blocks x %lld floats) but the "
+                 "built-in scratch holds %d bytes; use b200dp_tiny_mlp_fwd_bwd with caller-provided scratch",
+                 need, g, d.flat_numel + 1, B200DP_TINY_NOALLOC_SCRATCH_BYTES);
+  int dev = 0;
+  B200DP_CUDA_OK(cudaGetDevice(&dev));
+  B200DP_REQUIRE(dev >= 0 && dev < kMaxDevices, "tiny_mlp_noalloc: device ordinal %d out of range", dev);
+  void* scratch = nullptr;
+  if (int rc = noalloc_setup(dev, &scratch)) return rc;
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  // Nets that need more than the default 48 KB of dynamic shared memory: opt in to the kernel's
+  // full budget.  Always the maximum, never less, so this cannot shrink a limit that
+  // b200dp_tiny_mlp_fwd_bwd set for itself.
+  if (smem > 48 * 1024)
+    B200DP_CUDA_OK(cudaFuncSetAttribute(tiny_mlp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  // the ticket counter is the only part of the shared array that must start at zero
+  B200DP_CUDA_OK(cudaMemsetAsync(scratch, 0, sizeof(unsigned int), s));
+  unsigned int* ticket = reinterpret_cast<unsigned int*>(scratch);
+  float* part = reinterpret_cast<float*>(reinterpret_cast<char*>(scratch) + 256);
+  const float inv_count = 1.0f / (float(rows) * float(d.sizes[d.num_layers]));
+  tiny_mlp_kernel<<<g, kThreads, smem, s>>>(d, params, x, y, rows, inv_count, grads, loss, part, ticket);
   B200DP_CUDA_OK(cudaGetLastError());
   return B200DP_OK;
 }

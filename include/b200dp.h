@@ -78,6 +78,20 @@ int b200dp_tiny_mlp_fwd_bwd(const b200dp_mlp_desc* m, const float* params, const
                             int rows, float* grads, float* loss, void* scratch, long long scratch_bytes,
                             void* stream);
 
+/* Allocation-free variant of b200dp_tiny_mlp_fwd_bwd (no counterpart in the reference: the reference
+ * never manages device memory at all).  For callers that cannot call cudaMalloc where they train -
+ * a latency-critical loop, a plugin inside a framework whose pool owns the whole GPU, a process on
+ * a fixed memory budget.  The caller passes inputs and outputs only; the cross-block scratch is a
+ * built-in device array of B200DP_TINY_NOALLOC_SCRATCH_BYTES that every GPU using the library holds
+ * until exit.  Problems that need more scratch (256 + blocks*(flat_numel+1)*4 bytes, blocks <= SM
+ * count, 0 when one block suffices) are refused with an error.  The array is shared by all calls:
+ * calls that may overlap on one GPU race - serialise them.  The first call on each device looks up
+ * the array's device address (cudaGetSymbolAddress); make that first call before any stream
+ * capture.  Calls no cudaMalloc/cudaFree. */
+#define B200DP_TINY_NOALLOC_SCRATCH_BYTES (1 << 20)
+int b200dp_tiny_mlp_fwd_bwd_noalloc(const b200dp_mlp_desc* m, const float* params, const float* x,
+                                    const float* y, int rows, float* grads, float* loss, void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * Fused MSE loss + gradient (nn.MSELoss() + MseLossBackward, ref.py:94,173,176):
  *   *loss = mean((pred-target)^2),  dy = 2 (pred-target) / numel.
