@@ -44,7 +44,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--max-mb", type=float, default=1024)
     ap.add_argument("--dtype", choices=("fp32", "bf16"), default="bf16")
-    ap.add_argument("--blocks", type=int, default=32)
+    ap.add_argument("--blocks", type=int, default=0)
     ap.add_argument("--out", default=None)
     ap.add_argument("--with-gather-root", action="store_true")
     args = ap.parse_args()

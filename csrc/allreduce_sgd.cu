@@ -35,7 +35,7 @@ namespace b200dp {
 namespace {
 
 constexpr int kMaxBlocks = B200DP_SYNC_MAX_BLOCKS;
-constexpr int kSyncThreads = 512;
+constexpr int kSyncThreads = 256;   // 256 x <=128 regs: co-resident with a persistent GEMM CTA on the same SM
 
 struct SyncArgs {
   int rank, world;
@@ -86,36 +86,47 @@ __device__ __forceinline__ void peer_barrier(const SyncArgs& a, int block, uint3
 template <typename G> struct Vec;
 template <> struct Vec<float> {
   static constexpr int N = 4;
-  __device__ static void load(const void* base, long long i, float (&o)[4]) {
-    const float4 v = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(base) + i);
-    o[0] = v.x; o[1] = v.y; o[2] = v.z; o[3] = v.w;
+  __device__ static uint4 load(const void* base, long long i) {
+    return *reinterpret_cast<const uint4*>(reinterpret_cast<const float*>(base) + i);
+  }
+  __device__ static void unpack(const uint4& v, float (&o)[4]) {
+    o[0] = __uint_as_float(v.x); o[1] = __uint_as_float(v.y); o[2] = __uint_as_float(v.z); o[3] = __uint_as_float(v.w);
   }
 };
 template <> struct Vec<__nv_bfloat16> {
   static constexpr int N = 8;
-  __device__ static void load(const void* base, long long i, float (&o)[8]) {
-    const uint4 v = *reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(base) + i);
+  __device__ static uint4 load(const void* base, long long i) {
+    return *reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(base) + i);
+  }
+  __device__ static void unpack(const uint4& v, float (&o)[8]) {
     o[0] = bf16_lo(v.x); o[1] = bf16_hi(v.x); o[2] = bf16_lo(v.y); o[3] = bf16_hi(v.y);
     o[4] = bf16_lo(v.z); o[5] = bf16_hi(v.z); o[6] = bf16_lo(v.w); o[7] = bf16_hi(v.w);
   }
 };
 
-// reduce one vector of VN elements at index i over all ranks, in rank order
-template <typename G>
-__device__ __forceinline__ void reduce_vec(const SyncArgs& a, long long i, float (&acc)[Vec<G>::N]) {
-  constexpr int VN = Vec<G>::N;
-  float part[B200DP_MAX_RANKS][VN];
+// 16-byte loads of one vector from every rank's gradient buffer; issued back to back so that all
+// (N-1) NVLink round trips of this vector - and of the other unrolled vectors - overlap.
+template <typename G, int WR>
+__device__ __forceinline__ void load_all_ranks(const SyncArgs& a, long long i, uint4 (&raw)[WR]) {
 #pragma unroll
-  for (int r = 0; r < B200DP_MAX_RANKS; ++r)
-    if (r < a.world) Vec<G>::load(a.grads[r], i, part[r]);        // all peer loads in flight together
+  for (int r = 0; r < WR; ++r)
+    if (r < a.world) raw[r] = Vec<G>::load(a.grads[r], i);
+}
+
+// fixed rank order 0..N-1, fp32 accumulation, then the division (ref.py:193-197)
+template <typename G, int WR>
+__device__ __forceinline__ void reduce_raw(const SyncArgs& a, const uint4 (&raw)[WR], float (&acc)[Vec<G>::N]) {
+  constexpr int VN = Vec<G>::N;
 #pragma unroll
   for (int j = 0; j < VN; ++j) acc[j] = 0.0f;
 #pragma unroll
-  for (int r = 0; r < B200DP_MAX_RANKS; ++r) {
+  for (int r = 0; r < WR; ++r) {
     if (r < a.world) {
+      float part[VN];
+      Vec<G>::unpack(raw[r], part);
       const float w = a.w[r];
 #pragma unroll
-      for (int j = 0; j < VN; ++j) acc[j] = (w == 1.0f) ? acc[j] + part[r][j] : fmaf(w, part[r][j], acc[j]);
+      for (int j = 0; j < VN; ++j) acc[j] = (w == 1.0f) ? acc[j] + part[j] : fmaf(w, part[j], acc[j]);
     }
   }
 #pragma unroll
@@ -180,7 +191,9 @@ __device__ __forceinline__ void store_shadow(__nv_bfloat16* dst, const float (&p
   }
 }
 
-template <typename G>
+// WR = compile-time ceiling of the world size (2, 4 or 8), U = vectors in flight per thread; the
+// launcher picks U*WR = 16, i.e. sixteen 16-byte loads outstanding per thread whatever the world.
+template <typename G, int WR, int U>
 __device__ void sync_body(const SyncArgs& a, int block, int nblocks) {
   constexpr int VN = Vec<G>::N;
   const uint32_t epoch = a.epochs[block];
@@ -193,41 +206,62 @@ __device__ void sync_body(const SyncArgs& a, int block, int nblocks) {
     u_hi = units * (a.rank + 1) / a.world;
   }
   const bool has_shadow = a.shadow[a.rank] != nullptr;
-  for (long long u = u_lo + (long long)block * blockDim.x + threadIdx.x; u < u_hi;
-       u += (long long)nblocks * blockDim.x) {
-    const long long i = u * VN;
-    float g[VN], p[VN];
-    if (a.mode == 2) nvls_reduce_vec<G>(a, i, g);
-    else reduce_vec<G>(a, i, g);
-    sgd_vec<VN>(a, i, g, p);
-    if (a.mode == 0) {
-      store_master<VN>(a.params[a.rank] + i, p);
-      if (has_shadow) store_shadow<VN>(a.shadow[a.rank] + i, p);
-    } else if (a.mode == 1) {
-      store_master<VN>(a.params[a.rank] + i, p);
+  const long long step = (long long)nblocks * blockDim.x * U;
+  for (long long u0 = u_lo + (long long)block * blockDim.x * U + threadIdx.x; u0 < u_hi; u0 += step) {
+    float g[U][VN];
+    if (a.mode == 2) {
 #pragma unroll
-      for (int r = 0; r < B200DP_MAX_RANKS; ++r) {
-        if (r < a.world) {
-          if (a.push_master && r != a.rank) store_master<VN>(a.params[r] + i, p);
-          if (has_shadow) store_shadow<VN>(a.shadow[r] + i, p);
-        }
+      for (int k = 0; k < U; ++k) {
+        const long long u = u0 + (long long)k * blockDim.x;
+        if (u < u_hi) nvls_reduce_vec<G>(a, u * VN, g[k]);
       }
     } else {
-      store_master<VN>(a.params[a.rank] + i, p);
-      if (a.push_master) {
+      uint4 raw[U][WR];
 #pragma unroll
-        for (int j = 0; j < VN; j += 4)
-          asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(a.mc_params + i + j),
-                       "f"(p[j]), "f"(p[j + 1]), "f"(p[j + 2]), "f"(p[j + 3]) : "memory");
+      for (int k = 0; k < U; ++k) {
+        const long long u = u0 + (long long)k * blockDim.x;
+        if (u < u_hi) load_all_ranks<G, WR>(a, u * VN, raw[k]);
       }
-      if (has_shadow) {
-        if constexpr (VN == 8) {
-          asm volatile("multimem.st.relaxed.sys.global.v4.bf16x2 [%0], {%1,%2,%3,%4};" ::"l"(a.mc_shadow + i),
-                       "r"(pack_bf16x2(p[0], p[1])), "r"(pack_bf16x2(p[2], p[3])), "r"(pack_bf16x2(p[4], p[5])),
-                       "r"(pack_bf16x2(p[6], p[7])) : "memory");
-        } else {
-          asm volatile("multimem.st.relaxed.sys.global.v2.bf16x2 [%0], {%1,%2};" ::"l"(a.mc_shadow + i),
-                       "r"(pack_bf16x2(p[0], p[1])), "r"(pack_bf16x2(p[2], p[3])) : "memory");
+#pragma unroll
+      for (int k = 0; k < U; ++k) {
+        const long long u = u0 + (long long)k * blockDim.x;
+        if (u < u_hi) reduce_raw<G, WR>(a, raw[k], g[k]);
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < U; ++k) {
+      const long long u = u0 + (long long)k * blockDim.x;
+      if (u >= u_hi) continue;
+      const long long i = u * VN;
+      float p[VN];
+      sgd_vec<VN>(a, i, g[k], p);
+      store_master<VN>(a.params[a.rank] + i, p);
+      if (a.mode == 0) {
+        if (has_shadow) store_shadow<VN>(a.shadow[a.rank] + i, p);
+      } else if (a.mode == 1) {
+#pragma unroll
+        for (int r = 0; r < WR; ++r) {
+          if (r < a.world) {
+            if (a.push_master && r != a.rank) store_master<VN>(a.params[r] + i, p);
+            if (has_shadow) store_shadow<VN>(a.shadow[r] + i, p);
+          }
+        }
+      } else {
+        if (a.push_master) {
+#pragma unroll
+          for (int j = 0; j < VN; j += 4)
+            asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(a.mc_params + i + j),
+                         "f"(p[j]), "f"(p[j + 1]), "f"(p[j + 2]), "f"(p[j + 3]) : "memory");
+        }
+        if (has_shadow) {
+          if constexpr (VN == 8) {
+            asm volatile("multimem.st.relaxed.sys.global.v4.bf16x2 [%0], {%1,%2,%3,%4};" ::"l"(a.mc_shadow + i),
+                         "r"(pack_bf16x2(p[0], p[1])), "r"(pack_bf16x2(p[2], p[3])), "r"(pack_bf16x2(p[4], p[5])),
+                         "r"(pack_bf16x2(p[6], p[7])) : "memory");
+          } else {
+            asm volatile("multimem.st.relaxed.sys.global.v2.bf16x2 [%0], {%1,%2};" ::"l"(a.mc_shadow + i),
+                         "r"(pack_bf16x2(p[0], p[1])), "r"(pack_bf16x2(p[2], p[3])) : "memory");
+          }
         }
       }
     }
@@ -237,20 +271,27 @@ __device__ void sync_body(const SyncArgs& a, int block, int nblocks) {
   if (threadIdx.x == 0) a.epochs[block] = epoch + 2;
 }
 
-template <typename G>
-__global__ void __launch_bounds__(kSyncThreads)
+template <typename G, int WR, int U>
+__global__ void __launch_bounds__(kSyncThreads, 2)
 sync_kernel(const __grid_constant__ SyncArgs a) {
-  sync_body<G>(a, blockIdx.x, gridDim.x);
+  sync_body<G, WR, U>(a, blockIdx.x, gridDim.x);
 }
 
 // All ranks of a world emulated inside ONE cooperative launch on ONE GPU (blockIdx.y = rank):
 // the blocks really do wait on one another through the same signal pads, which exercises the
 // protocol on a single-GPU box.  Never launch the real kernel once per rank on one GPU - separate
 // launches are not guaranteed to be co-resident.
-template <typename G>
-__global__ void __launch_bounds__(kSyncThreads)
+template <typename G, int WR, int U>
+__global__ void __launch_bounds__(kSyncThreads, 2)
 sync_emulated_kernel(const SyncArgs* __restrict__ all) {
-  sync_body<G>(all[blockIdx.y], blockIdx.x, gridDim.x);
+  sync_body<G, WR, U>(all[blockIdx.y], blockIdx.x, gridDim.x);
+}
+
+template <typename G>
+const void* pick_kernel(int world, bool emulated) {
+  if (world <= 2) return emulated ? (const void*)sync_emulated_kernel<G, 2, 6> : (const void*)sync_kernel<G, 2, 6>;
+  if (world <= 4) return emulated ? (const void*)sync_emulated_kernel<G, 4, 4> : (const void*)sync_kernel<G, 4, 4>;
+  return emulated ? (const void*)sync_emulated_kernel<G, 8, 2> : (const void*)sync_kernel<G, 8, 2>;
 }
 
 // ---- standalone barrier and broadcast ------------------------------------------------------------
@@ -263,7 +304,7 @@ __global__ void barrier_kernel(const __grid_constant__ SyncArgs a) {
 // Every rank pulls `bytes` from root's copy of a peer-mapped buffer into its own (ref.py:87-88:
 // comm.bcast(state_dict) + load_state_dict).  a.params[] carries the buffer table.
 __global__ void __launch_bounds__(kSyncThreads)
-broadcast_kernel(const __grid_constant__ SyncArgs a, int root, long long n16) {
+broadcast_kernel(const __grid_constant__ SyncArgs a, int root, long long n16) {  // 256 threads
   const uint32_t epoch = a.epochs[blockIdx.x];
   peer_barrier(a, blockIdx.x, epoch + 1);
   if (a.rank != root) {
@@ -322,7 +363,7 @@ int pick_blocks(const b200dp_sync_args* in) {
   long long units = in->n / vn;
   if (in->mode != 0) units = (units + in->world - 1) / in->world;
   long long b = (units + kSyncThreads - 1) / kSyncThreads;
-  int cap = in->max_blocks > 0 ? in->max_blocks : 32;
+  int cap = in->max_blocks > 0 ? in->max_blocks : sm_count();   // default: one comm CTA per SM
   if (cap > kMaxBlocks) cap = kMaxBlocks;
   if (b < 1) b = 1;
   return int(b > cap ? cap : b);
@@ -338,9 +379,9 @@ extern "C" int b200dp_allreduce_sgd(const b200dp_sync_args* in, void* stream) {
   if (int rc = fill_args(in, &a)) return rc;
   const int blocks = pick_blocks(in);
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-  if (in->grads_bf16) sync_kernel<__nv_bfloat16><<<blocks, kSyncThreads, 0, s>>>(a);
-  else sync_kernel<float><<<blocks, kSyncThreads, 0, s>>>(a);
-  B200DP_CUDA_OK(cudaGetLastError());
+  const void* kern = in->grads_bf16 ? pick_kernel<__nv_bfloat16>(in->world, false) : pick_kernel<float>(in->world, false);
+  void* kargs[] = {(void*)&a};
+  B200DP_CUDA_OK(cudaLaunchKernel(kern, dim3(blocks), dim3(kSyncThreads), kargs, 0, s));
   return B200DP_OK;
 }
 
@@ -362,14 +403,13 @@ extern "C" int b200dp_allreduce_sgd_emulated(const b200dp_sync_args* per_rank, i
   const int blocks = pick_blocks(&per_rank[0]);
   int occ = 0;
   const bool bf = per_rank[0].grads_bf16 != 0;
-  if (bf) B200DP_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, sync_emulated_kernel<__nv_bfloat16>, kSyncThreads, 0));
-  else B200DP_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, sync_emulated_kernel<float>, kSyncThreads, 0));
+  const void* kern = bf ? pick_kernel<__nv_bfloat16>(world, true) : pick_kernel<float>(world, true);
+  B200DP_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kSyncThreads, 0));
   B200DP_REQUIRE(blocks * world <= occ * sm_count(), "sync_emulated: %d x %d blocks cannot be co-resident", blocks, world);
   const SyncArgs* dargs = reinterpret_cast<const SyncArgs*>(device_args);
   void* kargs[] = {(void*)&dargs};
   dim3 grid(blocks, world);
-  if (bf) B200DP_CUDA_OK(cudaLaunchCooperativeKernel((void*)sync_emulated_kernel<__nv_bfloat16>, grid, dim3(kSyncThreads), kargs, 0, s));
-  else B200DP_CUDA_OK(cudaLaunchCooperativeKernel((void*)sync_emulated_kernel<float>, grid, dim3(kSyncThreads), kargs, 0, s));
+  B200DP_CUDA_OK(cudaLaunchCooperativeKernel(kern, grid, dim3(kSyncThreads), kargs, 0, s));
   return B200DP_OK;
 }
 
@@ -404,7 +444,7 @@ extern "C" int b200dp_broadcast(const b200dp_sync_args* in, int root, long long 
   if (int rc = fill_args(&tmp, &a)) return rc;
   long long n16 = bytes / 16;
   long long b = (n16 + kSyncThreads - 1) / kSyncThreads;
-  const int blocks = int(b > 32 ? 32 : (b < 1 ? 1 : b));
+  const int blocks = int(b > kMaxBlocks ? kMaxBlocks : (b < 1 ? 1 : b));
   broadcast_kernel<<<blocks, kSyncThreads, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a, root, n16);
   B200DP_CUDA_OK(cudaGetLastError());
   return B200DP_OK;

@@ -141,7 +141,7 @@ int b200dp_cast_f32_bf16(const float* src, void* dst, long long n, void* stream)
  * u32, set to 1+peer when a peer does not arrive within timeout_ms.
  * All ranks must issue the same sequence of calls with the same n / mode / max_blocks.
  */
-#define B200DP_SYNC_MAX_BLOCKS 64
+#define B200DP_SYNC_MAX_BLOCKS 160
 
 typedef struct b200dp_sync_args {
   int rank, world;
@@ -161,7 +161,7 @@ typedef struct b200dp_sync_args {
   long long n;                           /* bucket length in elements (multiple of 8) */
   int mode;
   int push_master;                       /* modes 1/2: also write fp32 params into the peers */
-  int max_blocks;                        /* 0 = default (32); SM budget of the comm kernel */
+  int max_blocks;                        /* 0 = one CTA per SM; SM budget of the comm kernel */
   int timeout_ms;                        /* 0 = wait forever */
   const void* mc_grads;                  /* NVLS multicast addresses (mode 2) */
   void* mc_shadow;

@@ -9,7 +9,7 @@ import torch
 from . import _lib
 from ._lib import MAX_RANKS, c_float, c_int, c_ll, c_void_p
 
-SYNC_MAX_BLOCKS = 64
+SYNC_MAX_BLOCKS = 160
 MODES = {"fused_oneshot": 0, "fused_twoshot": 1, "fused_nvls": 2}
 FLAG_BYTES = SYNC_MAX_BLOCKS * MAX_RANKS * 4
 

@@ -54,7 +54,7 @@ def main():
         out["rows"] = t.shard.rows
         out["fingerprint"] = t.flat.fingerprint()
         t.close()
-    print("RESULT " + json.dumps(out))
+    sys.stdout.write("\nRESULT " + json.dumps(out) + "\n")     # one write: ranks share the pipe
     sys.stdout.flush()
     import torch.distributed as dist
     dist.barrier()

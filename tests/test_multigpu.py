@@ -20,7 +20,8 @@ def _run(n, scenario, timeout=600):
            os.path.join(ROOT, "tests", "mgpu_worker.py"), scenario]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, cwd=ROOT)
     assert r.returncode == 0, (r.stdout[-3000:], r.stderr[-3000:])
-    res = [json.loads(l[7:]) for l in r.stdout.splitlines() if l.startswith("RESULT ")]
+    import re
+    res = [json.loads(m) for m in re.findall(r"RESULT (\{.*?\})(?=\s|RESULT|$)", r.stdout)]
     assert len(res) == n
     return sorted(res, key=lambda d: d["rank"])
 
