@@ -39,7 +39,22 @@ struct GemmParams {
   int relu;
   int d_fp32;
   int num_m_blocks, num_n_blocks;
+  int group_m;          // rasterisation: tiles are visited in bands of group_m row-blocks
 };
+
+// Tile index -> (row block, column block).  Consecutive tiles (= the CTAs of one wave) walk down
+// a band of `group_m` row blocks before moving to the next column block, so a wave of 148 CTAs
+// touches ~16 row blocks x ~9 column blocks: both operand panels stay L2-resident instead of
+// streaming the whole A matrix through L2 once per wave.
+__device__ __forceinline__ void tile_coords(const GemmParams& p, int t, int& m_blk, int& n_blk) {
+  const int per_group = p.group_m * p.num_n_blocks;
+  const int g = t / per_group;
+  const int r = t - g * per_group;
+  const int m_first = g * p.group_m;
+  const int gsize = min(p.group_m, p.num_m_blocks - m_first);
+  n_blk = r / gsize;
+  m_blk = m_first + (r - n_blk * gsize);
+}
 
 template <int BN>
 struct Smem {
@@ -114,8 +129,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       int stage = 0;
       uint32_t phase = 0;
       for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-        const int m0 = (t % p.num_m_blocks) * BM;
-        const int n0 = (t / p.num_m_blocks) * BN;
+        int m_blk, n_blk;
+        tile_coords(p, t, m_blk, n_blk);
+        const int m0 = m_blk * BM;
+        const int n0 = n_blk * BN;
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = smem + stage * S::kStageBytes;
@@ -178,8 +195,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
       const int as = it & 1;
       const uint32_t aphase = (it >> 1) & 1;
-      const int m0 = (t % p.num_m_blocks) * BM;
-      const int n0 = (t / p.num_m_blocks) * BN;
+      int m_blk, n_blk;
+      tile_coords(p, t, m_blk, n_blk);
+      const int m0 = m_blk * BM;
+      const int n0 = n_blk * BN;
       const int row = m0 + quad * 32 + lane;
       mbar_wait(&tmem_full[as], aphase);
       tc_fence_after();
@@ -320,6 +339,7 @@ int launch(const b200dp_gemm_args* a, cudaStream_t stream) {
   p.relu = a->relu; p.d_fp32 = a->d_fp32;
   p.num_m_blocks = (a->M + BM - 1) / BM;
   p.num_n_blocks = (a->N + BN - 1) / BN;
+  p.group_m = 16;
   const int tiles = p.num_m_blocks * p.num_n_blocks;
   int grid = a->max_ctas > 0 ? a->max_ctas : sm_count();
   if (grid > tiles) grid = tiles;

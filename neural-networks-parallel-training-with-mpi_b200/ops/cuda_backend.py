@@ -52,6 +52,7 @@ class TinyCompute:
         self.scratch = K.scratch(K.tiny_mlp_scratch_bytes(flat.spec, max(max_rows, 1)), dev)
         self.loss = torch.zeros((), dtype=torch.float32, device=dev)
         self.bucket_hook: Optional[Callable[[int], None]] = None
+        self.aux_stream = None
 
     def prepare_batch(self, x, y):
         return x.to(torch.float32).contiguous(), y.to(torch.float32).contiguous()
@@ -110,6 +111,9 @@ class GemmCompute:
         widest = max(spec.sizes[1:])
         self.colsum_scratch = K.scratch(K.colsum_scratch_bytes(R, _align(widest, 8)), dev)
         self.bucket_hook: Optional[Callable[[int], None]] = None
+        self.aux_stream = None            # side stream shared with the sync strategy (bias-grad column sums)
+        self._ev_dy = torch.cuda.Event()
+        self._ev_colsum = torch.cuda.Event()
         self.gemm_max_ctas = 0
 
     def prepare_batch(self, x, y):
@@ -165,11 +169,12 @@ class GemmCompute:
             yhat, dy = self.yhat[:rows], self.dyb[:rows]
             gemm.linear_fwd(h, self._w(last), flat.bias(last), relu=False, out=yhat, max_ctas=self.gemm_max_ctas)
             K.mse_loss_grad(yhat, y, dy, self.loss, self.mse_scratch)
+            self._bias_grad(dy, last)
             gemm.linear_wgrad(dy, h, out=self._gw(last), max_ctas=self.gemm_max_ctas)
-            K.colsum(dy, self._gb(last), self.colsum_scratch)
             dnext = None
             if last > 0:
                 dnext = self._d(last, rows, self.spec.sizes[last])
+                self._wait_bias_grad()
                 gemm.linear_dgrad(dy, self._w(last), h, out=dnext, max_ctas=self.gemm_max_ctas)
         if self.bucket_hook is not None:
             self.bucket_hook(last)
@@ -177,14 +182,35 @@ class GemmCompute:
         for l in range(L - 2, -1, -1):
             dy_l = dnext                                   # dLoss/d(pre-activation of layer l), [rows, sizes[l+1]]
             a_in = x if l == 0 else self.acts[l][:rows]
+            self._bias_grad(dy_l, l)
             gemm.linear_wgrad(dy_l, a_in, out=self._gw(l), max_ctas=self.gemm_max_ctas)
-            K.colsum(dy_l, self._gb(l), self.colsum_scratch)
             if l > 0:
                 dnext = self._d(l, rows, self.spec.sizes[l])
+                self._wait_bias_grad()
                 gemm.linear_dgrad(dy_l, self._w(l), a_in, out=dnext, max_ctas=self.gemm_max_ctas)
             if self.bucket_hook is not None:
                 self.bucket_hook(l)
         return self.loss
+
+    def _bias_grad(self, dy, l) -> None:
+        """db_l = column sums of dY_l.  HBM-bound and independent of the GEMMs that follow, so it
+        runs on the side stream (ordered before that layer's sync kernel, which is queued there)."""
+        aux = self.aux_stream
+        if aux is None:
+            K.colsum(dy, self._gb(l), self.colsum_scratch)
+            return
+        main = torch.cuda.current_stream()
+        self._ev_dy.record(main)
+        aux.wait_event(self._ev_dy)
+        K.colsum(dy, self._gb(l), self.colsum_scratch, stream=aux)
+        self._ev_colsum.record(aux)
+        self._colsum_pending = True
+
+    def _wait_bias_grad(self) -> None:
+        # the d-buffers ping-pong: the next dgrad overwrites the buffer colsum is still reading
+        if self.aux_stream is not None and getattr(self, "_colsum_pending", False):
+            torch.cuda.current_stream().wait_event(self._ev_colsum)
+            self._colsum_pending = False
 
     @torch.no_grad()
     def predict(self, x) -> torch.Tensor:
@@ -226,30 +252,88 @@ def make_buckets(spec: MLPSpec, bucket_mb: float, elem_bytes: int) -> List[Bucke
     return out
 
 
-class CudaLocalSync(GradSync):
-    """World of one: the fused SGD kernel over the flat buffers."""
-    name = "cuda_local"
+class BucketedSync(GradSync):
+    """Common schedule of every GPU sync strategy: the step's gradient buffer is cut into buckets
+    (one per layer by default); as soon as backward has produced a bucket (``bucket_ready``, called
+    from inside the compute backend) its sync+update is queued on a side stream and overlaps the
+    rest of backward; ``sync_and_step`` queues whatever is left and joins the streams."""
+
+    def __init__(self, comm, weights, divisor, flat: FlatMLP, buckets: List[Bucket], overlap: bool):
+        super().__init__(comm, weights, divisor)
+        self.flat, self.buckets, self.overlap = flat, buckets, overlap
+        self.comm_stream = torch.cuda.Stream(device=flat.device) if overlap else None
+        self._ready = torch.cuda.Event()
+        self._done = torch.cuda.Event()
+        self._launched = set()
+        self._lr = self._mu = None
+        self._by_lo = {b.lo_layer: i for i, b in enumerate(buckets)}
+
+    def _run_bucket(self, b: Bucket, lr: float, mu: float, stream) -> None:
+        raise NotImplementedError
+
+    # called by the compute backend right after layer `l`'s backward has been queued
+    def bucket_ready(self, l: int) -> None:
+        i = self._by_lo.get(l)
+        if i is None or self._lr is None:
+            return
+        self._launch(i)
+
+    def _launch(self, i: int) -> None:
+        if i in self._launched:
+            return
+        main = torch.cuda.current_stream()
+        if self.comm_stream is not None:
+            self._ready.record(main)
+            self.comm_stream.wait_event(self._ready)
+            self._run_bucket(self.buckets[i], self._lr, self._mu, self.comm_stream)
+        else:
+            self._run_bucket(self.buckets[i], self._lr, self._mu, main)
+        self._launched.add(i)
+
+    def begin_step(self, lr: float, mu: float) -> None:
+        self._lr, self._mu = lr, mu
+        self._launched.clear()
 
     def sync_and_step(self, flat, lr, mu):
-        K.sgd_momentum(flat.params, flat.grads, flat.momentum, flat.shadow, lr, mu, first_step=False,
-                       grad_scale=1.0)
+        if self._lr is None:
+            self.begin_step(lr, mu)
+        for i in range(len(self.buckets)):
+            self._launch(i)
+        if self.comm_stream is not None:
+            self._done.record(self.comm_stream)
+            torch.cuda.current_stream().wait_event(self._done)
+        self._lr = None
         flat.step_count += 1
 
 
-class NcclAllReduceSync(GradSync):
-    """Library baseline: ``torch.distributed.all_reduce`` (NCCL) on the gradient buffer, then the
-    local SGD kernel.  Measured against, not shipped as the product path."""
+class CudaLocalSync(BucketedSync):
+    """World of one: the fused SGD kernel per bucket (HBM-bound; hidden under backward's GEMMs)."""
+    name = "local"
+
+    def _run_bucket(self, b, lr, mu, stream):
+        f = self.flat
+        sl = slice(b.start, b.stop)
+        K.sgd_momentum(f.params[sl], f.grads[sl], f.momentum[sl], f.shadow[sl] if f.shadow is not None else None,
+                       lr, mu, first_step=False, grad_scale=1.0, stream=stream)
+
+
+class NcclAllReduceSync(BucketedSync):
+    """Library baseline: ``torch.distributed.all_reduce`` (NCCL) per bucket, then the local SGD
+    kernel.  Measured against, not shipped as the product path."""
     name = "allreduce"
 
-    def sync_and_step(self, flat, lr, mu):
+    def _run_bucket(self, b, lr, mu, stream):
         import torch.distributed as dist
+        f = self.flat
+        sl = slice(b.start, b.stop)
         w = self.weights[self.comm.rank]
-        if w != 1.0:
-            flat.grads.mul_(w)
-        dist.all_reduce(flat.grads, op=dist.ReduceOp.SUM)
-        K.sgd_momentum(flat.params, flat.grads, flat.momentum, flat.shadow, lr, mu, first_step=False,
-                       grad_scale=1.0 / self.divisor)
-        flat.step_count += 1
+        with torch.cuda.stream(stream):
+            g = f.grads[sl]
+            if w != 1.0:
+                g.mul_(w)
+            dist.all_reduce(g, op=dist.ReduceOp.SUM)
+        K.sgd_momentum(f.params[sl], f.grads[sl], f.momentum[sl], f.shadow[sl] if f.shadow is not None else None,
+                       lr, mu, first_step=False, grad_scale=1.0 / self.divisor, stream=stream)
 
 
 class CudaGatherRootSync(GradSync):
@@ -272,15 +356,14 @@ class CudaGatherRootSync(GradSync):
         flat.step_count += 1
 
 
-class FusedSync(GradSync):
-    """The product path: one fused all-reduce + SGD kernel per bucket over NVLink peer memory,
-    queued on a side stream as soon as backward has produced the bucket."""
+class FusedSync(BucketedSync):
+    """The product path: one fused all-reduce + SGD kernel per bucket over NVLink peer memory."""
 
     def __init__(self, comm, weights, divisor, mode: str, flat: FlatMLP, symm: "SymmLayout",
                  buckets: List[Bucket], overlap: bool, max_blocks: int, timeout_ms: int):
-        super().__init__(comm, weights, divisor)
+        super().__init__(comm, weights, divisor, flat, buckets, overlap)
         self.name = mode
-        self.flat, self.symm, self.buckets, self.overlap = flat, symm, buckets, overlap
+        self.symm = symm
         dev = flat.device
         self.epochs = torch.zeros(ar.SYNC_MAX_BLOCKS, dtype=torch.int32, device=dev)
         self.error_flag = torch.zeros(1, dtype=torch.int32, device=dev)
@@ -296,47 +379,9 @@ class FusedSync(GradSync):
             bf16, m, self.push_master, max_blocks, timeout_ms,
             symm.mc("grads"), symm.mc("shadow") if flat.shadow is not None else None, symm.mc("params"))
         self.sharded_master = (m != 0) and not self.push_master
-        self.comm_stream = torch.cuda.Stream(device=dev) if overlap else None
-        self._ready = torch.cuda.Event()
-        self._done = torch.cuda.Event()
-        self._launched = set()
-        self._lr = self._mu = None
-        self._by_lo = {b.lo_layer: i for i, b in enumerate(buckets)}
 
-    # called by the compute backend right after layer `l`'s backward has been queued
-    def bucket_ready(self, l: int) -> None:
-        i = self._by_lo.get(l)
-        if i is None or self._lr is None:
-            return
-        self._launch(i)
-
-    def _launch(self, i: int) -> None:
-        if i in self._launched:
-            return
-        b = self.buckets[i]
-        main = torch.cuda.current_stream()
-        if self.comm_stream is not None:
-            self._ready.record(main)
-            self.comm_stream.wait_event(self._ready)
-            ar.launch(self.args, b.start, b.stop - b.start, self._lr, self._mu, False, stream=self.comm_stream)
-        else:
-            ar.launch(self.args, b.start, b.stop - b.start, self._lr, self._mu, False, stream=main)
-        self._launched.add(i)
-
-    def begin_step(self, lr: float, mu: float) -> None:
-        self._lr, self._mu = lr, mu
-        self._launched.clear()
-
-    def sync_and_step(self, flat, lr, mu):
-        if self._lr is None:
-            self.begin_step(lr, mu)
-        for i in range(len(self.buckets)):
-            self._launch(i)
-        if self.comm_stream is not None:
-            self._done.record(self.comm_stream)
-            torch.cuda.current_stream().wait_event(self._done)
-        self._lr = None
-        flat.step_count += 1
+    def _run_bucket(self, b, lr, mu, stream):
+        ar.launch(self.args, b.start, b.stop - b.start, lr, mu, False, stream=stream)
 
     def check_errors(self) -> None:
         v = int(self.error_flag.item())
@@ -412,19 +457,22 @@ class CudaRuntime:
         if tiny:
             self.buckets = [Bucket(0, spec.num_layers - 1, 0, spec.flat_numel)]
         self.device_broadcast = None
+        overlap = cfg.overlap and not tiny
         if comm.size == 1:
-            self.sync: GradSync = CudaLocalSync(comm, weights, divisor)
+            self.sync: GradSync = CudaLocalSync(comm, weights, divisor, self.flat, self.buckets, overlap)
         elif fused:
             self.sync = FusedSync(comm, weights, divisor, sync_name, self.flat, self.symm, self.buckets,
-                                  overlap=cfg.overlap and not tiny, max_blocks=0, timeout_ms=cfg.watchdog_ms)
-            self.compute.bucket_hook = self.sync.bucket_ready
+                                  overlap=overlap, max_blocks=0, timeout_ms=cfg.watchdog_ms)
             self.device_broadcast = self._device_broadcast
         elif sync_name == "allreduce":
-            self.sync = NcclAllReduceSync(comm, weights, divisor)
+            self.sync = NcclAllReduceSync(comm, weights, divisor, self.flat, self.buckets, overlap)
         elif sync_name == "gather_root":
             self.sync = CudaGatherRootSync(comm, weights, divisor)
         else:
             raise ValueError(f"unknown sync mode {sync_name!r}")
+        if isinstance(self.sync, BucketedSync):
+            self.compute.bucket_hook = self.sync.bucket_ready
+            self.compute.aux_stream = self.sync.comm_stream
         self.sync_name = sync_name
 
     def _device_broadcast(self, params: torch.Tensor) -> None:
