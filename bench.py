@@ -55,6 +55,8 @@ def parse():
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--no-overlap", action="store_true")
     p.add_argument("--bucket-mb", type=float, default=0.0)
+    p.add_argument("--cuda-graph", choices=("auto", "on", "off"), default="auto",
+                   help="replay the step from a CUDA graph (auto: on for the launch-bound ref config)")
     return p.parse_args()
 
 
@@ -129,8 +131,11 @@ def run_ours(args, rank, world):
     K, W = args.steps, max(args.warmup, 3)
 
     # ---- kernel-only: inputs resident on the device -------------------------------------------
+    graphed = (args.cuda_graph == "on" or (args.cuda_graph == "auto" and args.config == "ref")) \
+        and t.capture_full_shard_step()
+    step = t.graph_step if graphed else (lambda: t.step(t.x, t.y))
     for _ in range(W):
-        t.step(t.x, t.y)
+        step()
     torch.cuda.synchronize()
     barrier(world)
     sampler = ClockSampler(torch.cuda.current_device()).start() if rank == 0 else None
@@ -139,11 +144,11 @@ def run_ours(args, rank, world):
     torch.cuda.synchronize()
     e0.record()
     for _ in range(K):
-        loss = t.step(t.x, t.y)
+        loss = step()
     e1.record()
     torch.cuda.synchronize()
     barrier(world)
-    launches = _lib.launches - l0
+    launches = (_lib.launches - l0) if not graphed else K * t._graph_launches
     ms = max_over_ranks(e0.elapsed_time(e1), world)
     clocks = sampler.stop() if sampler else {}
     chk = getattr(t.sync, "check_errors", None)
@@ -189,7 +194,7 @@ def run_ours(args, rank, world):
         "impl": "ours",
         "config": {"model": cfgd["name"], "global_batch": global_batch, "seq_len": None,
                    "parallelism": f"dp{world}", "sync": getattr(t._runtime, "sync_name", t.sync.name),
-                   "rows_per_gpu": rows_local, "params": spec.num_params,
+                   "rows_per_gpu": rows_local, "params": spec.num_params, "cuda_graph": bool(graphed),
                    "l2": "inputs+weights larger than L2 (no flush needed)" if args.config != "ref"
                    else "working set is 13 parameters: cache-resident by nature"},
         "clocks": {"sm_mhz": clocks.get("sm_mhz"), "sm_max_mhz": clocks.get("sm_max_mhz"),

@@ -128,8 +128,46 @@ class Trainer:
             self.sync.sync_and_step(self.flat, self.cfg.lr, self.cfg.momentum)
         return loss
 
+    # ------------------------------------------------------------------ CUDA graph
+    def capture_full_shard_step(self) -> bool:
+        """Captures one full-shard step (all of this step's kernels, both streams) into a CUDA graph
+        so that launch-bound models - the reference's 13-parameter net is two ~3 us kernels - replay
+        with a single driver call.  Only for full-shard batches (static input buffers)."""
+        if self.device.type != "cuda" or self.shard.rows == 0 or getattr(self, "_graph", None) is not None:
+            return getattr(self, "_graph", None) is not None
+        if self.plan.batch < self.shard.rows:
+            return False
+        flat = self.flat
+        keep = (flat.params.clone(), flat.momentum.clone(), flat.step_count,
+                flat.shadow.clone() if flat.shadow is not None else None)
+        torch.cuda.synchronize()
+        self.comm.barrier()
+        self.step(self.x, self.y)                       # warm-up: lazy one-time set-up happens here
+        torch.cuda.synchronize()
+        self.comm.barrier()
+        flat.params.copy_(keep[0]); flat.momentum.copy_(keep[1]); flat.step_count = keep[2]
+        if keep[3] is not None:
+            flat.shadow.copy_(keep[3])
+        torch.cuda.synchronize()
+        self.comm.barrier()
+        from .ops import _lib as _native
+        g = torch.cuda.CUDAGraph()
+        n0 = _native.launches
+        with torch.cuda.graph(g):
+            self._graph_loss = self.step(self.x, self.y)
+        self._graph_launches = _native.launches - n0     # kernels of ours inside one replay
+        flat.step_count = keep[2]
+        self._graph = g
+        return True
+
+    def graph_step(self) -> torch.Tensor:
+        self._graph.replay()
+        self.flat.step_count += 1
+        return self._graph_loss
+
     def train(self) -> List[Dict[str, Any]]:
         cfg = self.cfg
+        use_graph = cfg.cuda_graph and self.capture_full_shard_step()
         for epoch in range(self.start_epoch, cfg.nepochs):
             emit(epoch_banner(epoch), cfg.quiet)                                # ref.py:152
             t0 = time.perf_counter()
@@ -137,7 +175,7 @@ class Trainer:
             for idx in self.plan.epoch():                                       # ref.py:155
                 xb, yb = (self.x, self.y) if idx is None else \
                     (self.x[idx.to(self.x.device)], self.y[idx.to(self.y.device)])
-                loss = self.step(xb, yb)
+                loss = self.graph_step() if (use_graph and idx is None) else self.step(xb, yb)
             if loss is None:                                                    # rank owns no rows
                 self.flat.grads.zero_()
                 self.sync.sync_and_step(self.flat, cfg.lr, cfg.momentum)

@@ -76,3 +76,28 @@ def test_checkpoint_from_gpu_loads_into_plain_module(tmp_path):
     m.load_state_dict(torch.load(path, weights_only=False)["model"])
     x = torch.randn(4, 2)
     torch.testing.assert_close(m(x), t.predict(x).cpu(), rtol=1e-5, atol=1e-6)
+
+
+def test_cuda_graph_replay_matches_eager():
+    from b200dp.config import TrainConfig
+    from b200dp.engine import Trainer
+    t = Trainer(TrainConfig(quiet=True, cuda_graph=True, nepochs=5), device=torch.device("cuda"))
+    lg = [h["loss"] for h in t.train()]
+    assert t._graph is not None and t._graph_launches == 2
+    e = Trainer(TrainConfig(quiet=True, nepochs=5), device=torch.device("cuda"))
+    le = [h["loss"] for h in e.train()]
+    assert lg == le and lg[:3] == pytest.approx([2530.8320, 2526.6858, 2518.3696], rel=5e-6)
+    assert t.flat.fingerprint() == e.flat.fingerprint()
+
+
+def test_overlapped_and_serial_schedules_agree_bitwise():
+    from b200dp.config import TrainConfig
+    from b200dp.engine import Trainer
+    kw = dict(quiet=True, nepochs=4, hidden=[256, 128, 64], n_features=64, n_samples=2048, dtype="bf16",
+              data_source="randn", data_dist="local", scale="none", lr=0.01, noise=0.1)
+    a = Trainer(TrainConfig(**kw, overlap=True), device=torch.device("cuda"))
+    b = Trainer(TrainConfig(**kw, overlap=False), device=torch.device("cuda"))
+    la = [h["loss"] for h in a.train()]
+    lb = [h["loss"] for h in b.train()]
+    assert la == lb
+    assert a.flat.fingerprint() == b.flat.fingerprint()
