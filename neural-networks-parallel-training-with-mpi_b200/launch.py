@@ -60,8 +60,33 @@ def bind_device(info: RankInfo):
         n = torch.cuda.device_count()
         dev = info.local_rank % max(n, 1)
         torch.cuda.set_device(dev)
+        bind_cpu_near_gpu(dev)
         return torch.device("cuda", dev)
     return torch.device("cpu")
+
+
+def bind_cpu_near_gpu(dev: int) -> bool:
+    """Pins this process to the CPU cores NVML reports as local to its GPU, so pinned host batches
+    are allocated on the GPU's NUMA node and H2D copies do not cross the socket interconnect
+    (matters when 8 ranks feed 8 GPUs at once).  Best effort: silently skipped when NVML or the
+    affinity call is unavailable."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        import torch
+        uuid = torch.cuda.get_device_properties(dev).uuid
+        h = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + str(uuid)).encode())
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        cpus = {64 * i + b for i, w in enumerate(mask) for b in range(64) if (w >> b) & 1}
+        allowed = os.sched_getaffinity(0)
+        cpus &= allowed
+        if cpus and cpus != allowed:
+            os.sched_setaffinity(0, cpus)
+            return True
+    except Exception:
+        pass
+    return False
 
 
 def init_process_group(info: RankInfo, backend: Optional[str] = None, timeout_s: int = 600):

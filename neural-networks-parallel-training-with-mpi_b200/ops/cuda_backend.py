@@ -430,10 +430,15 @@ class CudaRuntime:
             raise ValueError("models beyond the fused SIMT kernel's size train on the tensor-core path: "
                              "pass --dtype bf16")
         sync_name = cfg.sync
-        if sync_name == "auto":
-            sync_name = "fused_twoshot" if comm.size > 1 else "local"
-            if comm.size > 1 and spec.flat_numel * 4 <= 256 * 1024:
-                sync_name = "fused_oneshot"
+        auto = sync_name == "auto"
+        if auto:
+            # measured on 8xB200 (profiles/allreduce_sweep_*): one-shot wins below ~256 KB, the
+            # NVSwitch reduction (NVLS) wins from 4 GPUs up, two-shot peer loads win at 2 GPUs
+            sync_name = "local"
+            if comm.size > 1:
+                sync_name = "fused_nvls" if comm.size >= 4 else "fused_twoshot"
+                if spec.flat_numel * 4 <= 256 * 1024:
+                    sync_name = "fused_oneshot"
         fused = comm.size > 1 and sync_name.startswith("fused")
         weights, divisor = weights_and_divisor(trainer.counts, cfg.grad_weighting)
         self.symm: Optional[SymmLayout] = None
@@ -442,7 +447,7 @@ class CudaRuntime:
             self.symm = SymmLayout(comm, dev, spec.flat_numel, grads_bf16, cfg.dtype == "bf16",
                                    multicast=(sync_name == "fused_nvls"))
             if sync_name == "fused_nvls" and self.symm.buf.mc_ptr is None:
-                if comm.rank == 0:
+                if comm.rank == 0 and not auto:
                     print("b200dp: NVLS multicast is not available on this box - using fused_twoshot")
                 sync_name = "fused_twoshot"
             self.flat = FlatMLP(spec, dev, cfg.dtype,

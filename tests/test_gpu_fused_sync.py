@@ -81,3 +81,22 @@ def test_fused_sync_sample_weights():
 @pytest.mark.parametrize("mode", [0, 1])
 def test_fused_sync_large_multiblock(mode):
     _run(4, 1 << 20, mode, torch.bfloat16, [1.0] * 4, 4.0, steps=2, max_blocks=16)
+
+
+def test_watchdog_flags_a_peer_that_never_arrives():
+    """Failure detection: a dead rank hangs the reference forever at comm.gather /
+    comm.recv (ref.py:185,203).  Here the spin is bounded: rank 0 of a 2-rank world is launched
+    alone (its peer never shows up), the kernel gives up after timeout_ms and raises the flag."""
+    from b200dp.ops import allreduce_sgd as ar
+    dev, n = "cuda", 1024
+    bufs = [torch.zeros(n, device=dev) for _ in range(2)]
+    flags = [torch.zeros(ar.SYNC_MAX_BLOCKS * 8, device=dev, dtype=torch.int32) for _ in range(2)]
+    mom = torch.zeros(n, device=dev)
+    epochs = torch.zeros(ar.SYNC_MAX_BLOCKS, device=dev, dtype=torch.int32)
+    err = torch.zeros(1, device=dev, dtype=torch.int32)
+    a = ar.make_args(0, 2, [b.data_ptr() for b in bufs], [b.data_ptr() for b in bufs], None,
+                     [f.data_ptr() for f in flags], mom.data_ptr(), epochs.data_ptr(), err.data_ptr(),
+                     [1.0, 1.0], 2.0, False, 0, True, 1, timeout_ms=50)
+    ar.launch(a, 0, n, 0.1, 0.9, False)
+    torch.cuda.synchronize()
+    assert int(err.item()) == 2          # 1 + index of the missing peer
