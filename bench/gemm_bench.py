@@ -43,17 +43,25 @@ def main():
     dw = torch.empty(N, K, device="cuda", dtype=torch.float32)
     fl = 2.0 * M * N * K
     rows = []
+    variants = [("1cta_n256", dict(cta_group=1, tile_n=256)), ("1cta_n128", dict(cta_group=1, tile_n=128)),
+                ("2cta", dict(cta_group=2))]
+    dwb = torch.empty(N, K, device="cuda", dtype=torch.bfloat16)
     for name, ours, lib in [
-        ("fwd  ", lambda: gemm.linear_fwd(x, w, b, True, out=y), lambda: torch.relu(torch.addmm(b.bfloat16(), x, w.t()))),
-        ("dgrad", lambda: gemm.linear_dgrad(dy, w, x, out=dx), lambda: (dy @ w) * (x > 0)),
-        ("wgrad", lambda: gemm.linear_wgrad(dy, x, out=dw), lambda: dy.t() @ x),
+        ("fwd  ", lambda **kw: gemm.linear_fwd(x, w, b, True, out=y, **kw), lambda: torch.relu(torch.addmm(b.bfloat16(), x, w.t()))),
+        ("dgrad", lambda **kw: gemm.linear_dgrad(dy, w, x, out=dx, **kw), lambda: (dy @ w) * (x > 0)),
+        ("wgrad", lambda **kw: gemm.linear_wgrad(dy, x, out=dwb, **kw), lambda: dy.t() @ x),
     ]:
-        med, best = timeit(ours)
         lmed, lbest = timeit(lib)
-        rows.append({"op": name.strip(), "M": M, "N": N, "K": K, "ours_ms": med, "ours_tflops": fl / med / 1e9,
-                     "ours_best_tflops": fl / best / 1e9, "torch_ms": lmed, "torch_tflops": fl / lmed / 1e9,
-                     "frac_of_measured_peak": fl / med / 1e9 / peak})
-        print(json.dumps(rows[-1]))
+        rec = {"op": name.strip(), "M": M, "N": N, "K": K, "torch_ms": lmed, "torch_tflops": fl / lmed / 1e9}
+        for vname, kw in variants:
+            try:
+                med, best = timeit(lambda: ours(**kw))
+                rec[vname + "_tflops"] = fl / med / 1e9
+                rec[vname + "_frac_of_measured_peak"] = fl / med / 1e9 / peak
+            except Exception as e:  # noqa: BLE001
+                rec[vname + "_error"] = str(e)[:200]
+        rows.append(rec)
+        print(json.dumps(rec))
     return rows
 
 

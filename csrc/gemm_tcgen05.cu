@@ -270,6 +270,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
   }
 
+  __syncwarp();                        // re-converge: only lane 0 of the producer / MMA warps ran a role loop
   tc_fence_before();
   __syncthreads();
   if (warp == 1) {
@@ -364,6 +365,9 @@ int dispatch_major(const b200dp_gemm_args* a, cudaStream_t s) {
 }
 
 }  // namespace
+
+int gemm_pair_dispatch(const b200dp_gemm_args* a, cudaStream_t s);   // gemm_tcgen05_2cta.cu
+
 }  // namespace b200dp
 
 extern "C" int b200dp_gemm_bf16(const b200dp_gemm_args* a, void* stream) {
@@ -383,6 +387,12 @@ extern "C" int b200dp_gemm_bf16(const b200dp_gemm_args* a, void* stream) {
   }
   if (a->bias) B200DP_REQUIRE((reinterpret_cast<uintptr_t>(a->bias) & 15) == 0, "gemm: bias must be 16-byte aligned");
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  B200DP_REQUIRE(a->cta_group >= 0 && a->cta_group <= 2, "gemm: cta_group must be 0, 1 or 2");
+  // auto: CTA pairs (256x256 tiles, measured 1.50-1.61 PFLOP/s vs 1.32-1.44 for single CTAs at
+  // 8192x4096x4096) whenever there are enough 256x256 tiles to occupy most of the 74 SM pairs
+  const long long tiles2 = (long long)((a->M + 255) / 256) * ((a->N + 255) / 256);
+  const bool pair = a->cta_group == 2 || (a->cta_group == 0 && a->tile_n == 0 && tiles2 >= (3 * (sm_count() / 2)) / 4);
+  if (pair) return gemm_pair_dispatch(a, s);
   // 128x256 tiles unless the problem is too narrow to fill the machine with them
   const bool narrow = a->N <= 128 ||
                       ((long long)((a->M + 127) / 128) * ((a->N + 255) / 256) < sm_count() && a->N % 256 != 0);

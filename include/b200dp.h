@@ -54,6 +54,7 @@ typedef struct b200dp_gemm_args {
   long long ldmask;
   int tile_n;           /* 0 = auto, 128 or 256 */
   int max_ctas;         /* 0 = one persistent CTA per SM; >0 caps the grid (SM budget when overlapping) */
+  int cta_group;        /* 0 = auto; 1 = one CTA per 128x256 tile; 2 = CTA pair (cta_group::2) per 256x256 tile */
 } b200dp_gemm_args;
 
 int b200dp_gemm_bf16(const b200dp_gemm_args* args, void* stream);

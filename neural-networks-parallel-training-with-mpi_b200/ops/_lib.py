@@ -28,7 +28,7 @@ class GemmArgs(C.Structure):
         ("D", c_void_p), ("ldd", c_ll), ("d_fp32", c_int),
         ("bias", c_void_p), ("relu", c_int),
         ("mask_src", c_void_p), ("ldmask", c_ll),
-        ("tile_n", c_int), ("max_ctas", c_int),
+        ("tile_n", c_int), ("max_ctas", c_int), ("cta_group", c_int),
     ]
 
 

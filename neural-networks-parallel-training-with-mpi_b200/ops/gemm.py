@@ -16,7 +16,7 @@ def _check_bf16(t: torch.Tensor, name: str):
 
 def gemm(A: torch.Tensor, B: torch.Tensor, out: torch.Tensor, *, a_mn_major=False, b_mn_major=False,
          bias: Optional[torch.Tensor] = None, relu=False, mask_src: Optional[torch.Tensor] = None,
-         tile_n=0, max_ctas=0, stream=None) -> torch.Tensor:
+         tile_n=0, max_ctas=0, cta_group=0, stream=None) -> torch.Tensor:
     """``out[M,N] = epi(A[M,K] @ B[N,K]^T)``.  ``a_mn_major``: A is given as its transpose ``[K,M]``;
     ``b_mn_major``: B is given as ``[K,N]``."""
     _check_bf16(A, "A")
@@ -32,7 +32,7 @@ def gemm(A: torch.Tensor, B: torch.Tensor, out: torch.Tensor, *, a_mn_major=Fals
                       D=out.data_ptr(), ldd=out.stride(0), d_fp32=int(out.dtype == torch.float32),
                       bias=_lib.ptr(bias), relu=int(relu), mask_src=_lib.ptr(mask_src),
                       ldmask=mask_src.stride(0) if mask_src is not None else 0,
-                      tile_n=tile_n, max_ctas=max_ctas)
+                      tile_n=tile_n, max_ctas=max_ctas, cta_group=cta_group)
     _lib.check(_lib.lib().b200dp_gemm_bf16(C.byref(a), _lib.stream_ptr(stream)))
     _lib.count()
     return out

@@ -66,3 +66,36 @@ def test_strided_views_and_errors():
     _close(got, x.float() @ w.float().t(), 256)
     with pytest.raises(B200dpError):
         gemm.linear_fwd(_rand((64, 64)), _rand((12, 64)), None, relu=False)   # N % 8 != 0
+
+
+# ---- CTA-pair (cta_group::2) variant: same contract, 256x256 tiles over two SMs ----
+@pytest.mark.parametrize("M,N,K", [(256, 256, 64), (512, 512, 256), (200, 136, 72), (1000, 776, 1032),
+                                   (8192, 4096, 4096)])
+def test_pair_forward(M, N, K):
+    from b200dp.ops import gemm
+    torch.manual_seed(0)
+    x, w = _rand((M, K)), _rand((N, K), K ** -0.5)
+    b = torch.randn(N, device="cuda")
+    got = gemm.linear_fwd(x, w, b, relu=True, cta_group=2)
+    _close(got, torch.relu(x.float() @ w.float().t() + b), K)
+
+
+@pytest.mark.parametrize("M,N,K", [(256, 256, 64), (512, 256, 384), (200, 136, 72), (4096, 4096, 4096)])
+def test_pair_dgrad(M, N, K):
+    from b200dp.ops import gemm
+    torch.manual_seed(1)
+    dy, w = _rand((M, N)), _rand((N, K), N ** -0.5)
+    x = torch.relu(_rand((M, K)))
+    got = gemm.linear_dgrad(dy, w, x, cta_group=2)
+    _close(got, (dy.float() @ w.float()) * (x.float() > 0), N)
+
+
+@pytest.mark.parametrize("M,N,K", [(256, 256, 64), (512, 256, 384), (328, 136, 72), (8192, 4096, 4096)])
+@pytest.mark.parametrize("out_dtype", [torch.float32, torch.bfloat16])
+def test_pair_wgrad(M, N, K, out_dtype):
+    from b200dp.ops import gemm
+    torch.manual_seed(2)
+    dy, x = _rand((M, N), M ** -0.5), _rand((M, K))
+    out = torch.empty(N, K, dtype=out_dtype, device="cuda")
+    got = gemm.linear_wgrad(dy, x, out=out, cta_group=2)
+    _close(got, dy.float().t() @ x.float(), M)
