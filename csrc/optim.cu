@@ -53,6 +53,20 @@ cast_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, long
     dst[i] = __float2bfloat16_rn(src[i]);
 }
 
+// dst[r, :] = src[idx[r], :] for rows of `row_bytes` bytes (multiple of 16): one warp per row.
+__global__ void __launch_bounds__(256)
+gather_rows_kernel(const uint4* __restrict__ src, long long src_ld16, const long long* __restrict__ idx, int rows,
+                   int row16, uint4* __restrict__ dst) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  const int nwarps = (gridDim.x * blockDim.x) >> 5;
+  for (int r = warp; r < rows; r += nwarps) {
+    const uint4* s = src + idx[r] * src_ld16;
+    uint4* d = dst + (long long)r * row16;
+    for (int c = lane; c < row16; c += 32) d[c] = __ldg(s + c);
+  }
+}
+
 inline int ew_grid(long long n) {
   long long g = (n + 255) / 256;
   const long long cap = 8ll * sm_count();
@@ -90,6 +104,24 @@ extern "C" int b200dp_cast_f32_bf16(const float* src, void* dst, long long n, vo
   B200DP_REQUIRE(((uintptr_t)src & 15) == 0 && ((uintptr_t)dst & 7) == 0, "cast: misaligned buffers");
   cast_kernel<<<ew_grid(n / 4 + 1), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
       src, reinterpret_cast<__nv_bfloat16*>(dst), n);
+  B200DP_CUDA_OK(cudaGetLastError());
+  return B200DP_OK;
+}
+
+// Mini-batch assembly on the device: dst[r,:] = src[idx[r],:].  Replaces the
+// DataLoader's index + default_collate on the host (ref.py:146,155) when batch < shard.
+extern "C" int b200dp_gather_rows(const void* src, long long src_row_bytes, const long long* idx, int rows,
+                                  long long row_bytes, void* dst, void* stream) {
+  B200DP_REQUIRE(src && idx && dst, "gather_rows: null pointer");
+  B200DP_REQUIRE(row_bytes > 0 && row_bytes % 16 == 0 && src_row_bytes % 16 == 0,
+                 "gather_rows: row sizes must be multiples of 16 bytes");
+  B200DP_REQUIRE(((uintptr_t)src & 15) == 0 && ((uintptr_t)dst & 15) == 0, "gather_rows: misaligned buffers");
+  if (rows <= 0) return B200DP_OK;
+  int grid = (rows + 7) / 8;
+  if (grid > 8 * sm_count()) grid = 8 * sm_count();
+  gather_rows_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const uint4*>(src), src_row_bytes / 16, idx, rows, int(row_bytes / 16),
+      reinterpret_cast<uint4*>(dst));
   B200DP_CUDA_OK(cudaGetLastError());
   return B200DP_OK;
 }

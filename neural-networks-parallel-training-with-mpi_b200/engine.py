@@ -128,6 +128,14 @@ class Trainer:
             self.sync.sync_and_step(self.flat, self.cfg.lr, self.cfg.momentum)
         return loss
 
+    def _minibatch(self, idx: torch.Tensor):
+        """Rows ``idx`` of the resident shard (ref.py:146,155: DataLoader shuffle + collate)."""
+        idx = idx.to(self.x.device)
+        if self.backend == "cuda":
+            from .ops import kernels as K
+            return K.gather_rows(self.x, idx), self.y.index_select(0, idx)
+        return self.x[idx], self.y[idx]
+
     # ------------------------------------------------------------------ CUDA graph
     def capture_full_shard_step(self) -> bool:
         """Captures one full-shard step (all of this step's kernels, both streams) into a CUDA graph
@@ -173,8 +181,7 @@ class Trainer:
             t0 = time.perf_counter()
             loss = None
             for idx in self.plan.epoch():                                       # ref.py:155
-                xb, yb = (self.x, self.y) if idx is None else \
-                    (self.x[idx.to(self.x.device)], self.y[idx.to(self.y.device)])
+                xb, yb = (self.x, self.y) if idx is None else self._minibatch(idx)
                 loss = self.graph_step() if (use_graph and idx is None) else self.step(xb, yb)
             if loss is None:                                                    # rank owns no rows
                 self.flat.grads.zero_()

@@ -110,7 +110,8 @@ class GemmCompute:
             self.mse_scratch = K.scratch(K.mse_scratch_bytes(R * self.nout), dev)
         widest = max(spec.sizes[1:])
         self.colsum_scratch = K.scratch(K.colsum_scratch_bytes(R, _align(widest, 8)), dev)
-        self.bucket_hook: Optional[Callable[[int], None]] = None
+        self.bucket_hook: Optional[Callable[..., None]] = None
+        self.wgrad_chunks = {}            # layer -> [(row0, row1), ...] of its weight (set with the buckets)
         self.aux_stream = None            # side stream shared with the sync strategy (bias-grad column sums)
         self._ev_dy = torch.cuda.Event()
         self._ev_colsum = torch.cuda.Event()
@@ -170,27 +171,40 @@ class GemmCompute:
             gemm.linear_fwd(h, self._w(last), flat.bias(last), relu=False, out=yhat, max_ctas=self.gemm_max_ctas)
             K.mse_loss_grad(yhat, y, dy, self.loss, self.mse_scratch)
             self._bias_grad(dy, last)
-            gemm.linear_wgrad(dy, h, out=self._gw(last), max_ctas=self.gemm_max_ctas)
             dnext = None
             if last > 0:
                 dnext = self._d(last, rows, self.spec.sizes[last])
                 self._wait_bias_grad()
                 gemm.linear_dgrad(dy, self._w(last), h, out=dnext, max_ctas=self.gemm_max_ctas)
-        if self.bucket_hook is not None:
+            self._wgrad_chunked(dy, h, last)
+        if self.head_is_gemv and self.bucket_hook is not None:
             self.bucket_hook(last)
         # ---- hidden layers, top down ----
         for l in range(L - 2, -1, -1):
             dy_l = dnext                                   # dLoss/d(pre-activation of layer l), [rows, sizes[l+1]]
             a_in = x if l == 0 else self.acts[l][:rows]
             self._bias_grad(dy_l, l)
-            gemm.linear_wgrad(dy_l, a_in, out=self._gw(l), max_ctas=self.gemm_max_ctas)
             if l > 0:
+                # dgrad first: it is on the critical path of backward, and it must have read W_l
+                # before the first chunk of this layer's sync is allowed to update W_l
                 dnext = self._d(l, rows, self.spec.sizes[l])
                 self._wait_bias_grad()
                 gemm.linear_dgrad(dy_l, self._w(l), a_in, out=dnext, max_ctas=self.gemm_max_ctas)
-            if self.bucket_hook is not None:
-                self.bucket_hook(l)
+            self._wgrad_chunked(dy_l, a_in, l)
         return self.loss
+
+    def _wgrad_chunked(self, dy, a_in, l) -> None:
+        """dW_l = dY^T a_in, one GEMM per row chunk of W_l; each chunk's bucket is handed to the sync
+        strategy as soon as its GEMM is queued."""
+        gw = self._gw(l)
+        chunks = self.wgrad_chunks.get(l) or [(0, gw.shape[0])]
+        for c, (r0, r1) in enumerate(chunks):
+            if len(chunks) == 1:
+                gemm.linear_wgrad(dy, a_in, out=gw, max_ctas=self.gemm_max_ctas)
+            else:
+                gemm.linear_wgrad(dy[:, r0:r1], a_in, out=gw[r0:r1], max_ctas=self.gemm_max_ctas)
+            if self.bucket_hook is not None:
+                self.bucket_hook(l, c)
 
     def _bias_grad(self, dy, l) -> None:
         """db_l = column sums of dY_l.  HBM-bound and independent of the GEMMs that follow, so it
@@ -227,28 +241,67 @@ class GemmCompute:
 # =============================================================================== sync strategies
 @dataclass
 class Bucket:
-    lo_layer: int
-    hi_layer: int
+    """A contiguous range of the flat buffers that is synchronised by one kernel.  ``layer`` /
+    ``chunk`` say which piece of backward completes it: chunk ``c`` of layer ``l`` covers the weight
+    rows ``[row0, row1)`` (the last chunk also carries the bias and the segment padding)."""
+    layer: int
+    chunk: int
     start: int
     stop: int
+    row0: int = 0
+    row1: int = 0
 
 
-def make_buckets(spec: MLPSpec, bucket_mb: float, elem_bytes: int) -> List[Bucket]:
-    """Per-layer buckets (bucket_mb == 0) or consecutive layers merged up to ``bucket_mb``; built top
-    layer first, the order backward completes them."""
+def _best_row_split(blocks: int, nb: int, units: int, kmax: int) -> List[int]:
+    """Splits ``blocks`` 256-row GEMM tile rows into <= kmax chunks (largest first, smallest last)
+    such that the total number of GEMM waves over ``units`` CTA pairs does not grow, preferring the
+    smallest last chunk (the part of the sync nothing can hide) and then more chunks."""
+    import itertools
+
+    def waves(b):
+        return -(-(b * nb) // units)
+
+    best = ([blocks], waves(blocks), blocks, 1)
+    for k in range(2, max(2, kmax) + 1):
+        if k > blocks:
+            break
+        for cuts in itertools.combinations(range(1, blocks), k - 1):
+            parts = [b - a for a, b in zip((0,) + cuts, cuts + (blocks,))]
+            if any(parts[i] < parts[i + 1] for i in range(k - 1)):
+                continue                                     # keep them non-increasing
+            w = sum(waves(p_) for p_ in parts)
+            cand = (parts, w, parts[-1], k)
+            if (w, cand[2], -k) < (best[1], best[2], -best[3]):
+                best = cand
+    return best[0]
+
+
+def make_buckets(spec: MLPSpec, bucket_mb: float, elem_bytes: int, units: int = 74) -> List[Bucket]:
+    """One bucket per layer; a layer whose gradient exceeds ``bucket_mb`` (default 32 MB) is cut into
+    row chunks of its weight matrix: the wgrad GEMM runs chunk by chunk and each chunk's sync starts
+    while the next chunk is still being computed.  That matters for the LAST layer of backward,
+    whose sync has nothing else to hide behind.  Chunk sizes are chosen so the chunked GEMMs need
+    no more waves over the ``units`` SM pairs than the unsplit GEMM.  Top layer first."""
+    limit = int((bucket_mb if bucket_mb > 0 else 32.0) * (1 << 20))
     out: List[Bucket] = []
-    limit = int(bucket_mb * (1 << 20))
-    cur: Optional[Bucket] = None
     for l in reversed(range(spec.num_layers)):
-        s, e = spec.layer_span(l)
-        if cur is not None and limit > 0 and (cur.stop - s) * elem_bytes <= limit:
-            cur.lo_layer, cur.start = l, s
-        else:
-            if cur is not None:
-                out.append(cur)
-            cur = Bucket(l, l, s, e)
-    if cur is not None:
-        out.append(cur)
+        s0, e0 = spec.layer_span(l)
+        wseg, _ = spec.layer_segments(l)
+        rows, cols = wseg.shape
+        want = -(-(wseg.numel * elem_bytes) // limit)
+        parts = [rows]
+        if want > 1 and rows >= 512:
+            blocks = -(-rows // 256)
+            parts = [p_ * 256 for p_ in _best_row_split(blocks, -(-cols // 256), units, min(4, want + 1))]
+            parts[-1] -= sum(parts) - rows                      # the last chunk takes the ragged tail
+            parts = [p_ for p_ in parts if p_ > 0]
+        r = 0
+        for c, n in enumerate(parts):
+            r1 = r + n
+            start = s0 + r * cols
+            stop = e0 if r1 == rows else s0 + r1 * cols
+            out.append(Bucket(l, c, start, stop, r, r1))
+            r = r1
     return out
 
 
@@ -266,17 +319,24 @@ class BucketedSync(GradSync):
         self._done = torch.cuda.Event()
         self._launched = set()
         self._lr = self._mu = None
-        self._by_lo = {b.lo_layer: i for i, b in enumerate(buckets)}
+        self._by_key = {(b.layer, b.chunk): i for i, b in enumerate(buckets)}
+        self.chunks_of = {}
+        for b in buckets:
+            self.chunks_of.setdefault(b.layer, []).append(b)
 
     def _run_bucket(self, b: Bucket, lr: float, mu: float, stream) -> None:
         raise NotImplementedError
 
-    # called by the compute backend right after layer `l`'s backward has been queued
-    def bucket_ready(self, l: int) -> None:
-        i = self._by_lo.get(l)
-        if i is None or self._lr is None:
+    # called by the compute backend right after chunk `c` of layer `l`'s backward has been queued
+    # (c = None: everything of that layer)
+    def bucket_ready(self, l: int, c: Optional[int] = None) -> None:
+        if self._lr is None:
             return
-        self._launch(i)
+        keys = [(l, c)] if c is not None else [(b.layer, b.chunk) for b in self.chunks_of.get(l, [])]
+        for k in keys:
+            i = self._by_key.get(k)
+            if i is not None:
+                self._launch(i)
 
     def _launch(self, i: int) -> None:
         if i in self._launched:
@@ -458,9 +518,10 @@ class CudaRuntime:
             self.flat = FlatMLP(spec, dev, cfg.dtype)
         max_rows = trainer.shard.rows
         self.compute = TinyCompute(self.flat, max_rows) if tiny else GemmCompute(self.flat, max_rows)
-        self.buckets = make_buckets(spec, cfg.bucket_mb, 2 if grads_bf16 else 4)
+        self.buckets = make_buckets(spec, cfg.bucket_mb, 2 if grads_bf16 else 4,
+                                    units=max(torch.cuda.get_device_properties(dev).multi_processor_count // 2, 1))
         if tiny:
-            self.buckets = [Bucket(0, spec.num_layers - 1, 0, spec.flat_numel)]
+            self.buckets = [Bucket(0, 0, 0, spec.flat_numel)]
         self.device_broadcast = None
         overlap = cfg.overlap and not tiny
         if comm.size == 1:
@@ -477,6 +538,9 @@ class CudaRuntime:
             raise ValueError(f"unknown sync mode {sync_name!r}")
         if isinstance(self.sync, BucketedSync):
             self.compute.bucket_hook = self.sync.bucket_ready
+            if not tiny:
+                self.compute.wgrad_chunks = {l: [(b.row0, b.row1) for b in bs]
+                                             for l, bs in self.sync.chunks_of.items()}
             self.compute.aux_stream = self.sync.comm_stream
         self.sync_name = sync_name
 

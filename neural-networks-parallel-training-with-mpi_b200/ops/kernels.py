@@ -29,6 +29,7 @@ _lib.register("b200dp_colsum_bf16", [c_void_p, c_ll, c_int, c_int, c_void_p, c_i
 _lib.register("b200dp_sgd_momentum", [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_ll, c_float, c_float,
                                       c_float, c_int, c_void_p])
 _lib.register("b200dp_cast_f32_bf16", [c_void_p, c_void_p, c_ll, c_void_p])
+_lib.register("b200dp_gather_rows", [c_void_p, c_ll, c_void_p, c_int, c_ll, c_void_p, c_void_p])
 
 
 def _fix_restypes(lib):
@@ -145,3 +146,21 @@ def sgd_momentum(params, grads, momentum, shadow, lr, mu, first_step, grad_scale
 def cast_f32_bf16(src, dst, stream=None):
     _lib.check(L().b200dp_cast_f32_bf16(src.data_ptr(), dst.data_ptr(), src.numel(), _lib.stream_ptr(stream)))
     _lib.count()
+
+
+def gather_rows(src, idx, dst=None, stream=None):
+    """``dst[r] = src[idx[r]]`` for a 2-D row-major tensor whose rows are a multiple of 16 bytes; other
+    shapes fall back to torch indexing (tiny rows such as the reference's 2 features)."""
+    row_bytes = src.shape[1] * src.element_size()
+    if src.dim() != 2 or row_bytes % 16 or (src.stride(0) * src.element_size()) % 16 or src.stride(1) != 1:
+        out = src.index_select(0, idx)
+        if dst is not None:
+            dst.copy_(out)
+            return dst
+        return out
+    if dst is None:
+        dst = torch.empty(idx.numel(), src.shape[1], dtype=src.dtype, device=src.device)
+    _lib.check(L().b200dp_gather_rows(src.data_ptr(), src.stride(0) * src.element_size(), idx.data_ptr(),
+                                      idx.numel(), row_bytes, dst.data_ptr(), _lib.stream_ptr(stream)))
+    _lib.count()
+    return dst

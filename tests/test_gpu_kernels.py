@@ -116,3 +116,21 @@ def test_cast():
     dst = torch.empty(src.numel(), device="cuda", dtype=torch.bfloat16)
     K.cast_f32_bf16(src, dst)
     assert torch.equal(dst, src.bfloat16())
+
+
+@pytest.mark.parametrize("dtype,cols", [(torch.bfloat16, 256), (torch.float32, 12), (torch.float32, 2)])
+def test_gather_rows(dtype, cols):
+    from b200dp.ops import kernels as K
+    src = torch.randn(1000, cols, device="cuda").to(dtype)
+    idx = torch.randperm(1000, device="cuda")[:333]
+    assert torch.equal(K.gather_rows(src, idx), src[idx])
+
+
+def test_minibatch_training_on_gpu_matches_cpu():
+    from b200dp.config import TrainConfig
+    from b200dp.engine import Trainer
+    kw = dict(quiet=True, nepochs=3, batch_size=4, use_batch_size=True, hidden=[8], n_features=4, n_samples=32,
+              lr=0.0003, scale="global", data_dist="local")
+    g = Trainer(TrainConfig(**kw), device=torch.device("cuda"))
+    c = Trainer(TrainConfig(**kw, backend="torch"), device=torch.device("cpu"))
+    assert [h["loss"] for h in g.train()] == pytest.approx([h["loss"] for h in c.train()], rel=1e-4)
