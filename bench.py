@@ -8,7 +8,7 @@ ranks.  Prints ONE JSON line on rank 0.
 
 --config wide (default)  BASELINE.json configs[2]: MLP 12288 -> 4x4096 -> 1 (100.7 M parameters), bf16,
                          8192 rows per GPU (weak scaling), synthetic linear-teacher data, random init.
---config deep            configs[3]: 4096 -> 16x8192 -> 1 (1.1 B parameters), bf16, 4096 rows per GPU.
+--config deep            configs[3]: 4096 -> 16x8192 -> 1 (1.04 B parameters), bf16, 8192 rows per GPU.
 --config ref             configs[0-1]: the reference's own 2-3-1 MLP on make_regression(16, 2) (strong
                          scaling: 16 rows in total, as hard-coded at ref.py:72).
 
@@ -36,7 +36,7 @@ sys.path.insert(0, ROOT)
 CONFIGS = {
     "wide": dict(n_features=12288, hidden=[4096] * 4, n_outputs=1, rows_per_gpu=8192, dtype="bf16",
                  scaling="weak", name="wide MLP 12288-4x4096-1 (100.7M params)"),
-    "deep": dict(n_features=4096, hidden=[8192] * 16, n_outputs=1, rows_per_gpu=4096, dtype="bf16",
+    "deep": dict(n_features=4096, hidden=[8192] * 16, n_outputs=1, rows_per_gpu=8192, dtype="bf16",
                  scaling="weak", name="deep MLP 4096-16x8192-1 (1.04B params)"),
     "ref": dict(n_features=2, hidden=[3], n_outputs=1, rows_total=16, dtype="fp32", scaling="strong",
                 name="reference MLP 2-3-1 on make_regression(16,2)"),

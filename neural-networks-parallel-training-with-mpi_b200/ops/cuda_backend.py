@@ -114,7 +114,8 @@ class GemmCompute:
         self.wgrad_chunks = {}            # layer -> [(row0, row1), ...] of its weight (set with the buckets)
         self.aux_stream = None            # side stream shared with the sync strategy (bias-grad column sums)
         self._ev_dy = torch.cuda.Event()
-        self._ev_colsum = torch.cuda.Event()
+        self._ev_colsum = [torch.cuda.Event(), torch.cuda.Event()]
+        self._colsum_pending = [False, False]
         self.gemm_max_ctas = 0
 
     def prepare_batch(self, x, y):
@@ -174,7 +175,6 @@ class GemmCompute:
             dnext = None
             if last > 0:
                 dnext = self._d(last, rows, self.spec.sizes[last])
-                self._wait_bias_grad()
                 gemm.linear_dgrad(dy, self._w(last), h, out=dnext, max_ctas=self.gemm_max_ctas)
             self._wgrad_chunked(dy, h, last)
         if self.head_is_gemv and self.bucket_hook is not None:
@@ -188,7 +188,7 @@ class GemmCompute:
                 # dgrad first: it is on the critical path of backward, and it must have read W_l
                 # before the first chunk of this layer's sync is allowed to update W_l
                 dnext = self._d(l, rows, self.spec.sizes[l])
-                self._wait_bias_grad()
+                self._wait_bias_grad(l)
                 gemm.linear_dgrad(dy_l, self._w(l), a_in, out=dnext, max_ctas=self.gemm_max_ctas)
             self._wgrad_chunked(dy_l, a_in, l)
         return self.loss
@@ -217,14 +217,17 @@ class GemmCompute:
         self._ev_dy.record(main)
         aux.wait_event(self._ev_dy)
         K.colsum(dy, self._gb(l), self.colsum_scratch, stream=aux)
-        self._ev_colsum.record(aux)
-        self._colsum_pending = True
+        self._ev_colsum[l & 1].record(aux)
+        self._colsum_pending[l & 1] = True
 
-    def _wait_bias_grad(self) -> None:
-        # the d-buffers ping-pong: the next dgrad overwrites the buffer colsum is still reading
-        if self.aux_stream is not None and getattr(self, "_colsum_pending", False):
-            torch.cuda.current_stream().wait_event(self._ev_colsum)
-            self._colsum_pending = False
+    def _wait_bias_grad(self, l: int) -> None:
+        """The d-buffers ping-pong: dgrad of layer l writes the buffer that the column-sum of layer
+        l+1 (queued a whole layer earlier on the side stream) has been reading.  Wait for THAT one -
+        not for layer l's own column-sum, which would put it on the critical path."""
+        k = (l + 1) & 1
+        if self.aux_stream is not None and self._colsum_pending[k]:
+            torch.cuda.current_stream().wait_event(self._ev_colsum[k])
+            self._colsum_pending[k] = False
 
     @torch.no_grad()
     def predict(self, x) -> torch.Tensor:

@@ -16,6 +16,11 @@ from b200dp.launch import bind_device, discover, init_process_group  # noqa: E40
 from b200dp.parallel.comm import world_comm  # noqa: E402
 
 
+class _Raw:
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+
+
 def main():
     scenario = sys.argv[1]
     info = discover()
@@ -47,6 +52,31 @@ def main():
         if comm.rank == 0:
             out["ckpt_norm"] = float(sum(v.double().norm() for v in torch.load(ck, weights_only=False)["model"].values()))
         t.close()
+    elif scenario == "barrier":
+        # K10: stream-ordered cross-GPU barrier.  Every rank publishes a value in its peer-mapped buffer,
+        # barriers on the stream, then reads every peer's value with a plain device copy.
+        from b200dp.ops import allreduce_sgd as ar
+        from b200dp.ops.cuda_backend import SymmLayout
+        symm = SymmLayout(comm, dev, 1024, False, False, multicast=False)
+        mine = symm.tensor("params", torch.float32)
+        epochs = torch.zeros(ar.SYNC_MAX_BLOCKS, dtype=torch.int32, device=dev)
+        err = torch.zeros(1, dtype=torch.int32, device=dev)
+        a = ar.make_args(comm.rank, comm.size, symm.ptrs("grads"), symm.ptrs("params"), None, symm.ptrs("flags"),
+                         mine.data_ptr(), epochs.data_ptr(), err.data_ptr(), [1.0] * comm.size, 1.0, False, 0,
+                         True, 1, 5000)
+        seen = []
+        for it in range(3):
+            mine.fill_(float(100 * it + comm.rank))
+            ar.peer_barrier(a)                       # everyone has written
+            peer = (comm.rank + 1) % comm.size
+            got = torch.empty(1, device=dev)
+            raw = torch.as_tensor(_Raw(symm.ptrs("params")[peer], 4), device=dev).view(torch.float32)
+            got.copy_(raw)
+            ar.peer_barrier(a)                       # everyone has read before the next overwrite
+            seen.append(float(got.item()))
+        out["seen"] = seen
+        out["err"] = int(err.item())
+        symm.buf.close()
     elif scenario.startswith("uneven_"):
         sync = scenario[7:]
         t = Trainer(TrainConfig(quiet=True, sync=sync, nepochs=3, n_samples=17, grad_weighting="samples"), comm, dev)

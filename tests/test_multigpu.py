@@ -47,6 +47,13 @@ def test_wide_fused_matches_nccl_baseline():
         assert got[0]["ckpt_norm"] == pytest.approx(base[0]["ckpt_norm"], rel=1e-3)
 
 
+def test_peer_barrier_orders_cross_gpu_writes():
+    res = _run(2, "barrier")
+    for r in res:
+        peer = (r["rank"] + 1) % 2
+        assert r["seen"] == [float(100 * it + peer) for it in range(3)] and r["err"] == 0
+
+
 def test_uneven_shards_sample_weighting():
     res = _run(2, "uneven_fused_oneshot")
     assert [r["rows"] for r in res] == [9, 8]
