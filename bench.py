@@ -134,11 +134,16 @@ def run_ours(args, rank, world):
     graphed = (args.cuda_graph == "on" or (args.cuda_graph == "auto" and args.config == "ref")) \
         and t.capture_full_shard_step()
     step = t.graph_step if graphed else (lambda: t.step(t.x, t.y))
+    # nvidia-smi needs ~100 ms to come up: start it before the warm-up and wait for its first line, so
+    # that it is sampling (every 50 ms) while the timed region runs
+    sampler = ClockSampler(torch.cuda.current_device(), period_ms=50).start() if rank == 0 else None
     for _ in range(W):
         step()
     torch.cuda.synchronize()
+    if sampler is not None:
+        sampler.wait_first_sample(2.0)
+        sampler.mark()
     barrier(world)
-    sampler = ClockSampler(torch.cuda.current_device()).start() if rank == 0 else None
     l0 = _lib.launches
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize()

@@ -496,10 +496,11 @@ class CudaRuntime:
         auto = sync_name == "auto"
         if auto:
             # measured on 8xB200 (profiles/allreduce_sweep_*): one-shot wins below ~256 KB, the
-            # NVSwitch reduction (NVLS) wins from 4 GPUs up, two-shot peer loads win at 2 GPUs
+            # NVSwitch reduction (NVLS) wins at 8 GPUs (834 vs 628 GB/s), two-shot peer loads win at
+            # 2 GPUs and tie at 4
             sync_name = "local"
             if comm.size > 1:
-                sync_name = "fused_nvls" if comm.size >= 4 else "fused_twoshot"
+                sync_name = "fused_nvls" if comm.size > 4 else "fused_twoshot"
                 if spec.flat_numel * 4 <= 256 * 1024:
                     sync_name = "fused_oneshot"
         fused = comm.size > 1 and sync_name.startswith("fused")

@@ -34,6 +34,17 @@ class ClockSampler:
         self._thr.start()
         return self
 
+    def wait_first_sample(self, timeout_s: float = 2.0) -> bool:
+        import time
+        t0 = time.time()
+        while not self._lines and time.time() - t0 < timeout_s:
+            time.sleep(0.01)
+        return bool(self._lines)
+
+    def mark(self) -> None:
+        """Samples before this point (warm-up) are dropped from the summary."""
+        self._skip = len(self._lines)
+
     def stop(self) -> Dict:
         if self._proc is not None:
             self._proc.terminate()
@@ -48,7 +59,8 @@ class ClockSampler:
     def summary(self) -> Dict:
         sm, mx, power, reasons = [], [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for line in self._lines:
+        lines = self._lines[getattr(self, "_skip", 0):] or self._lines[-1:]
+        for line in lines:
             parts = [p.strip() for p in line.split(",")]
             if len(parts) < 9:
                 continue
