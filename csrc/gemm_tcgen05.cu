@@ -346,7 +346,10 @@ int launch(const b200dp_gemm_args* a, cudaStream_t stream) {
   if (grid > tiles) grid = tiles;
 
   auto kern = gemm_bf16_kernel<BN, A_MN, B_MN>;
-  static bool attr_set = false;
+  static bool attr_set_dev[64] = {false};     // per device: the attribute belongs to the device's context
+  int dev_ = 0;
+  cudaGetDevice(&dev_);
+  bool& attr_set = attr_set_dev[dev_ & 63];
   if (!attr_set) {
     B200DP_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal));
     attr_set = true;

@@ -374,7 +374,10 @@ int launch_pair(const b200dp_gemm_args* a, cudaStream_t stream) {
   if (clusters < 1) clusters = 1;
   if (clusters > tiles) clusters = tiles;
   auto kern = gemm_bf16_pair_kernel<A_MN, B_MN>;
-  static bool attr_set = false;
+  static bool attr_set_dev[64] = {false};     // per device: the attribute belongs to the device's context
+  int dev_ = 0;
+  cudaGetDevice(&dev_);
+  bool& attr_set = attr_set_dev[dev_ & 63];
   if (!attr_set) {
     B200DP_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
     attr_set = true;

@@ -204,7 +204,10 @@ extern "C" int b200dp_tiny_mlp_fwd_bwd(const b200dp_mlp_desc* m, const float* pa
   const long long need = g > 1 ? 256 + (long long)g * (d.flat_numel + 1) * 4 : 0;
   B200DP_REQUIRE(g == 1 || (scratch != nullptr && scratch_bytes >= need),
                  "tiny_mlp: scratch too small (%lld < %lld bytes)", scratch_bytes, need);
-  static int attr_smem = 0;
+  static int attr_smem_dev[64] = {0};          // per device: the attribute belongs to the device's context
+  int dev_ = 0;
+  cudaGetDevice(&dev_);
+  int& attr_smem = attr_smem_dev[dev_ & 63];
   if (smem > attr_smem) {
     B200DP_CUDA_OK(cudaFuncSetAttribute(tiny_mlp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     attr_smem = smem;

@@ -122,10 +122,18 @@ class Trainer:
         begin = getattr(self.sync, "begin_step", None)
         if begin is not None:                      # fused sync: buckets are queued from inside backward
             begin(self.cfg.lr, self.cfg.momentum)
+        nvtx = self.device.type == "cuda" and self.cfg.log_jsonl is not None
+        if nvtx:
+            torch.cuda.nvtx.range_push("fwd_bwd")
         with self.timer.phase("fwd_bwd"):
             loss = self.compute.loss_and_grads(x, y)
+        if nvtx:
+            torch.cuda.nvtx.range_pop()
+            torch.cuda.nvtx.range_push("sync_update")
         with self.timer.phase("sync_update"):
             self.sync.sync_and_step(self.flat, self.cfg.lr, self.cfg.momentum)
+        if nvtx:
+            torch.cuda.nvtx.range_pop()
         return loss
 
     def _minibatch(self, idx: torch.Tensor):
