@@ -165,12 +165,12 @@ __device__ __forceinline__ void sgd_vec(const SyncArgs& a, long long i, const fl
     float4 m4;
     if (a.first) m4 = make_float4(g[j], g[j + 1], g[j + 2], g[j + 3]);
     else {
-      m4 = *reinterpret_cast<float4*>(mom + j);
+      m4 = __ldcs(reinterpret_cast<const float4*>(mom + j));
       m4.x = fmaf(a.mu, m4.x, g[j]); m4.y = fmaf(a.mu, m4.y, g[j + 1]);
       m4.z = fmaf(a.mu, m4.z, g[j + 2]); m4.w = fmaf(a.mu, m4.w, g[j + 3]);
     }
-    *reinterpret_cast<float4*>(mom + j) = m4;
-    float4 p4 = *reinterpret_cast<float4*>(par + j);
+    __stcs(reinterpret_cast<float4*>(mom + j), m4);      // streaming: keep the GEMMs' panels in L2
+    float4 p4 = __ldcs(reinterpret_cast<const float4*>(par + j));
     p4.x -= a.lr * m4.x; p4.y -= a.lr * m4.y; p4.z -= a.lr * m4.z; p4.w -= a.lr * m4.w;
     p[j] = p4.x; p[j + 1] = p4.y; p[j + 2] = p4.z; p[j + 3] = p4.w;
   }

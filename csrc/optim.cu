@@ -20,24 +20,26 @@ sgd_kernel(float* __restrict__ p, const void* __restrict__ g, float* __restrict_
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
     float4 gv;
     if (GRAD_BF16) {
-      const uint2 u = reinterpret_cast<const uint2*>(g)[i];
+      const uint2 u = __ldcs(reinterpret_cast<const uint2*>(g) + i);
       gv = make_float4(bf16_lo(u.x), bf16_hi(u.x), bf16_lo(u.y), bf16_hi(u.y));
     } else {
-      gv = reinterpret_cast<const float4*>(g)[i];
+      gv = __ldcs(reinterpret_cast<const float4*>(g) + i);
     }
     gv.x *= scale; gv.y *= scale; gv.z *= scale; gv.w *= scale;
     float4 mv;
     if (first) mv = gv;
     else {
-      mv = reinterpret_cast<float4*>(m)[i];
+      mv = __ldcs(reinterpret_cast<const float4*>(m) + i);
       mv.x = fmaf(mu, mv.x, gv.x); mv.y = fmaf(mu, mv.y, gv.y);
       mv.z = fmaf(mu, mv.z, gv.z); mv.w = fmaf(mu, mv.w, gv.w);
     }
-    reinterpret_cast<float4*>(m)[i] = mv;
-    float4 pv = reinterpret_cast<float4*>(p)[i];
+    // streaming (evict-first) accesses: this kernel moves 20 B/parameter through L2 while GEMMs
+    // run on the other stream; it must not push their operand panels out of L2
+    __stcs(reinterpret_cast<float4*>(m) + i, mv);
+    float4 pv = __ldcs(reinterpret_cast<const float4*>(p) + i);
     pv.x -= lr * mv.x; pv.y -= lr * mv.y; pv.z -= lr * mv.z; pv.w -= lr * mv.w;
-    reinterpret_cast<float4*>(p)[i] = pv;
-    if (shadow) reinterpret_cast<uint2*>(shadow)[i] = make_uint2(pack_bf16x2(pv.x, pv.y), pack_bf16x2(pv.z, pv.w));
+    __stcs(reinterpret_cast<float4*>(p) + i, pv);
+    if (shadow) __stcs(reinterpret_cast<uint2*>(shadow) + i, make_uint2(pack_bf16x2(pv.x, pv.y), pack_bf16x2(pv.z, pv.w)));
   }
 }
 

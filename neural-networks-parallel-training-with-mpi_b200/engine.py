@@ -309,6 +309,13 @@ class Trainer:
         if len(set(prints)) != 1:
             raise RuntimeError(f"replicas diverged: parameter fingerprints {prints}")
 
+    def state_dict(self):
+        """Full fp32 ``state_dict`` (reference key names) valid on every rank: collects the master
+        slices first when the optimizer state is sharded across ranks (bf16 two-shot / NVLS)."""
+        if self._runtime is not None:
+            self._runtime.gather_optimizer_state()
+        return self.flat.state_dict()
+
     def save_checkpoint(self, path: str, epoch: int) -> None:
         if self._runtime is not None:
             self._runtime.gather_optimizer_state()

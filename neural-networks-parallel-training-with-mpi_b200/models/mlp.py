@@ -183,8 +183,11 @@ class FlatMLP:
         return m
 
     def fingerprint(self) -> int:
-        """Order-sensitive 64-bit hash of the parameter bytes (replica-equality checks)."""
-        b = self.params.detach().to("cpu").contiguous().view(torch.uint8).numpy().tobytes()
+        """Order-sensitive 64-bit hash of the bytes every replica computes with (replica-equality
+        checks): the bf16 shadow weights in bf16 mode - the fp32 master of a slice may live only on
+        its owner rank there - else the fp32 parameters."""
+        src = self.shadow if self.shadow is not None else self.params
+        b = src.detach().to("cpu").contiguous().view(torch.uint8).numpy().tobytes()
         import hashlib
 
         return int.from_bytes(hashlib.blake2b(b, digest_size=8).digest(), "little")

@@ -11,7 +11,7 @@ import threading
 from typing import Optional
 
 _PKG = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-LIB_PATH = os.path.join(_PKG, "lib", "libb200dp.so")
+LIB_PATH = os.environ.get("B200DP_LIB") or os.path.join(_PKG, "lib", "libb200dp.so")   # override: A/B builds
 _lock = threading.Lock()
 _lib: Optional[C.CDLL] = None
 

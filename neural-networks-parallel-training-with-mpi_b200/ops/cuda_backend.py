@@ -255,7 +255,12 @@ class Bucket:
     row1: int = 0
 
 
-def _best_row_split(blocks: int, nb: int, units: int, kmax: int) -> List[int]:
+MIN_CHUNK_BLOCKS = 4     # >= 1024 weight rows per chunk: every chunk GEMM re-reads the whole activation
+                         # matrix, so small chunks turn HBM-bound (measured: a 256-row chunk of the
+                         # 4096x12288 wgrad ran at 0.43 PFLOP/s, profiles/timeline_wide_n1.md)
+
+
+def _best_row_split(blocks: int, nb: int, units: int, kmax: int, min_blocks: int = MIN_CHUNK_BLOCKS) -> List[int]:
     """Splits ``blocks`` 256-row GEMM tile rows into <= kmax chunks (largest first, smallest last)
     such that the total number of GEMM waves over ``units`` CTA pairs does not grow, preferring the
     smallest last chunk (the part of the sync nothing can hide) and then more chunks."""
@@ -270,8 +275,8 @@ def _best_row_split(blocks: int, nb: int, units: int, kmax: int) -> List[int]:
             break
         for cuts in itertools.combinations(range(1, blocks), k - 1):
             parts = [b - a for a, b in zip((0,) + cuts, cuts + (blocks,))]
-            if any(parts[i] < parts[i + 1] for i in range(k - 1)):
-                continue                                     # keep them non-increasing
+            if any(parts[i] < parts[i + 1] for i in range(k - 1)) or parts[-1] < min_blocks:
+                continue                                     # non-increasing, no HBM-bound slivers
             w = sum(waves(p_) for p_ in parts)
             cand = (parts, w, parts[-1], k)
             if (w, cand[2], -k) < (best[1], best[2], -best[3]):
@@ -295,7 +300,7 @@ def make_buckets(spec: MLPSpec, bucket_mb: float, elem_bytes: int, units: int = 
         parts = [rows]
         if want > 1 and rows >= 512:
             blocks = -(-rows // 256)
-            parts = [p_ * 256 for p_ in _best_row_split(blocks, -(-cols // 256), units, min(4, want + 1))]
+            parts = [p_ * 256 for p_ in _best_row_split(blocks, -(-cols // 256), units, min(3, want))]
             parts[-1] -= sum(parts) - rows                      # the last chunk takes the ragged tail
             parts = [p_ for p_ in parts if p_ > 0]
         r = 0

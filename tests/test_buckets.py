@@ -38,7 +38,7 @@ def test_large_first_layer_is_chunked_small_layers_are_not():
     assert len(per_layer[0]) > 1 and len(per_layer[1]) == 1 and len(per_layer[2]) == 1
     assert [b.layer for b in bs] == sorted([b.layer for b in bs], reverse=True)      # backward order
     last = per_layer[0][-1]
-    assert last.row1 - last.row0 <= 1024                                              # small exposed tail
+    assert 1024 <= last.row1 - last.row0 <= 1536                                      # small, but not HBM-bound, tail
     assert len(make_buckets(MLPSpec([12288, 4096, 1]), 1e6, 2)) == 2                 # limit disables chunking
 
 

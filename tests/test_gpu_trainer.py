@@ -101,3 +101,27 @@ def test_overlapped_and_serial_schedules_agree_bitwise():
     lb = [h["loss"] for h in b.train()]
     assert la == lb
     assert a.flat.fingerprint() == b.flat.fingerprint()
+
+
+def test_host_fed_training_equals_resident_training():
+    """fit_host_batches (pinned host batches, H2D per step, lagged loss read-back) must produce exactly
+    the losses and parameters of stepping on the resident shard."""
+    from b200dp.config import TrainConfig
+    from b200dp.engine import Trainer
+    kw = dict(quiet=True, nepochs=0, hidden=[256, 128], n_features=64, n_samples=1024, dtype="bf16",
+              data_source="randn", data_dist="local", scale="none", lr=0.01, noise=0.1)
+    a = Trainer(TrainConfig(**kw), device=torch.device("cuda"))
+    b = Trainer(TrainConfig(**kw), device=torch.device("cuda"))
+    xh = a.shard.x.to(torch.bfloat16).pin_memory()
+    yh = a.shard.y.pin_memory()
+    la = a.fit_host_batches(iter([(xh, yh)] * 6), 6)
+    lb = []
+    for _ in range(6):
+        lb.append(float(b.step(b.x, b.y).item()))
+    assert la == lb and len(la) == 6
+    assert a.flat.fingerprint() == b.flat.fingerprint()
+    assert a.h2d_bytes_per_step == xh.numel() * 2 + yh.numel() * 4 and a.d2h_bytes_per_step == 4
+    # fp32 host batches are accepted too (cast on the device)
+    c = Trainer(TrainConfig(**kw), device=torch.device("cuda"))
+    lc = c.fit_host_batches(iter([(a.shard.x.pin_memory(), yh)] * 2), 2)
+    assert lc == la[:2]
