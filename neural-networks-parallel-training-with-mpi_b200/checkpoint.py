@@ -28,7 +28,7 @@ def save_checkpoint(path: str, flat, epoch: int, config: Dict[str, Any], extra: 
         "momentum": flat.momentum_state(),
         "epoch": int(epoch),
         "step_count": int(flat.step_count),
-        "sizes": list(flat.spec.sizes),
+        "sizes": list(flat.spec.logical_sizes),
         "config": dict(config),
         "rng": torch.random.get_rng_state(),
     }
@@ -50,8 +50,8 @@ def load_checkpoint(path: str, flat, strict_sizes: bool = True) -> Dict[str, Any
     payload = torch.load(path, map_location="cpu", weights_only=False)
     if isinstance(payload, dict) and "model" not in payload:
         payload = {"model": payload}                     # a bare state_dict (e.g. from the reference's MLP)
-    if strict_sizes and "sizes" in payload and tuple(payload["sizes"]) != tuple(flat.spec.sizes):
-        raise ValueError(f"checkpoint is for sizes {payload['sizes']}, model has {list(flat.spec.sizes)}")
+    if strict_sizes and "sizes" in payload and tuple(payload["sizes"]) != tuple(flat.spec.logical_sizes):
+        raise ValueError(f"checkpoint is for sizes {payload['sizes']}, model has {list(flat.spec.logical_sizes)}")
     flat.load_state_dict(payload["model"])
     if "momentum" in payload:
         flat.load_momentum_state(payload["momentum"])

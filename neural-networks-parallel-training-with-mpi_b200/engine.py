@@ -269,8 +269,8 @@ class Trainer:
                 stage(i + 1)
             main.wait_event(ready[k])
             xd, yd = slots[k]
-            xb, yb = (xd, yd) if (xd.dtype == self.x.dtype and yd.dtype == self.y.dtype) \
-                else self.compute.prepare_batch(xd, yd)
+            xb, yb = (xd, yd) if (xd.dtype == self.x.dtype and yd.dtype == self.y.dtype
+                                  and xd.shape[1] == self.x.shape[1]) else self.compute.prepare_batch(xd, yd)
             loss = self.step(xb, yb)
             consumed[k].record(main)
             loss_host[i:i + 1].copy_(loss.reshape(1), non_blocking=True)

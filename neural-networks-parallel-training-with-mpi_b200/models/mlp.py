@@ -14,6 +14,7 @@ reference's own ``MLP``.
 """
 from __future__ import annotations
 
+import math
 from collections import OrderedDict
 from dataclasses import dataclass
 from typing import Dict, List, Optional, Sequence
@@ -48,7 +49,8 @@ class Segment:
     kind: str        # "weight" | "bias"
     offset: int      # elements into the flat buffers
     numel: int
-    shape: tuple
+    shape: tuple     # physical shape inside the flat buffers (feature sizes rounded up to `pad_to`)
+    logical_shape: tuple = ()   # the model's own shape (what state_dict exposes)
 
 
 def _round_up(x: int, m: int) -> int:
@@ -56,24 +58,35 @@ def _round_up(x: int, m: int) -> int:
 
 
 class MLPSpec:
-    def __init__(self, sizes: Sequence[int]):
+    """Layer sizes and the flat-buffer layout.  ``pad_to`` > 1 (the tensor-core path uses 8) rounds the
+    input and hidden widths up so every row of every matrix is a whole number of 16-byte vectors;
+    the padding rows / columns hold zeros, stay zero under training (their activations and
+    gradients are identically zero) and never appear in ``state_dict``.  ``sizes`` are the physical
+    (padded) widths the kernels see, ``logical_sizes`` the model's own."""
+
+    def __init__(self, sizes: Sequence[int], pad_to: int = 1):
         if len(sizes) < 2:
             raise ValueError("an MLP needs at least an input and an output size")
-        self.sizes = tuple(int(s) for s in sizes)
+        self.logical_sizes = tuple(int(s) for s in sizes)
+        self.pad_to = int(pad_to)
+        self.sizes = tuple(_round_up(s, self.pad_to) if i < len(sizes) - 1 else s
+                           for i, s in enumerate(self.logical_sizes))
         self.num_layers = len(self.sizes) - 1
         segs: List[Segment] = []
         off = 0
         for l in range(self.num_layers):
             fan_in, fan_out = self.sizes[l], self.sizes[l + 1]
-            for kind, shape in (("weight", (fan_out, fan_in)), ("bias", (fan_out,))):
+            lin, lout = self.logical_sizes[l], self.logical_sizes[l + 1]
+            for kind, shape, lshape in (("weight", (fan_out, fan_in), (lout, lin)), ("bias", (fan_out,), (lout,))):
                 n = 1
                 for s in shape:
                     n *= s
-                segs.append(Segment(f"layers.{2 * l}.{kind}", l, kind, off, n, shape))
+                segs.append(Segment(f"layers.{2 * l}.{kind}", l, kind, off, n, shape, lshape))
                 off = _round_up(off + n, ALIGN_ELEMS)
         self.segments = tuple(segs)
         self.flat_numel = off
-        self.num_params = sum(s.numel for s in segs)
+        self.num_params = sum(math.prod(s.logical_shape) for s in segs)
+        self.padded = self.sizes != self.logical_sizes
 
     def layer_segments(self, l: int):
         return self.segments[2 * l], self.segments[2 * l + 1]
@@ -109,6 +122,12 @@ class FlatMLP:
     def _view(self, flat: torch.Tensor, seg: Segment) -> torch.Tensor:
         return flat[seg.offset:seg.offset + seg.numel].view(seg.shape)
 
+    def _logical(self, flat: torch.Tensor, seg: Segment) -> torch.Tensor:
+        v = self._view(flat, seg)
+        if seg.shape == seg.logical_shape:
+            return v
+        return v[tuple(slice(0, n) for n in seg.logical_shape)]
+
     def weight(self, l: int, flat: Optional[torch.Tensor] = None) -> torch.Tensor:
         return self._view(self.params if flat is None else flat, self.spec.segments[2 * l])
 
@@ -129,7 +148,7 @@ class FlatMLP:
         gen_state = torch.random.get_rng_state()
         try:
             torch.manual_seed(seed)
-            ref = MLP(self.spec.sizes)
+            ref = MLP(self.spec.logical_sizes)
         finally:
             torch.random.set_rng_state(gen_state)
         self.load_state_dict(ref.state_dict())
@@ -138,11 +157,12 @@ class FlatMLP:
         """Same distribution (uniform +-1/sqrt(fan_in) for weight and bias), generated on the
         device: for billion-parameter models where a CPU init would dominate start-up."""
         g = torch.Generator(device=self.device).manual_seed(seed)
+        self.params.zero_()                                  # padding rows / columns must be zero
         for seg in self.spec.segments:
-            fan_in = self.spec.sizes[seg.layer]
+            fan_in = self.spec.logical_sizes[seg.layer]
             bound = 1.0 / (fan_in ** 0.5)
-            v = self._view(self.params, seg)
-            v.copy_((torch.rand(seg.shape, generator=g, device=self.device) * 2 - 1) * bound)
+            v = self._logical(self.params, seg)
+            v.copy_((torch.rand(seg.logical_shape, generator=g, device=self.device) * 2 - 1) * bound)
         self.sync_shadow()
 
     def sync_shadow(self) -> None:
@@ -153,7 +173,7 @@ class FlatMLP:
     def state_dict(self) -> "OrderedDict[str, torch.Tensor]":
         out = OrderedDict()
         for seg in self.spec.segments:
-            out[seg.key] = self._view(self.params, seg).detach().to("cpu", copy=True)
+            out[seg.key] = self._logical(self.params, seg).detach().to("cpu", copy=True).contiguous()
         return out
 
     def load_state_dict(self, sd: Dict[str, torch.Tensor]) -> None:
@@ -164,21 +184,23 @@ class FlatMLP:
             raise KeyError(f"state_dict mismatch: missing={missing} unexpected={extra}")
         for seg in self.spec.segments:
             t = sd[seg.key]
-            if tuple(t.shape) != tuple(seg.shape):
-                raise ValueError(f"{seg.key}: shape {tuple(t.shape)} != {seg.shape}")
-            self._view(self.params, seg).copy_(t.to(self.device, torch.float32))
+            if tuple(t.shape) != tuple(seg.logical_shape):
+                raise ValueError(f"{seg.key}: shape {tuple(t.shape)} != {seg.logical_shape}")
+            self._view(self.params, seg).zero_()
+            self._logical(self.params, seg).copy_(t.to(self.device, torch.float32))
         self.sync_shadow()
 
     def momentum_state(self) -> "OrderedDict[str, torch.Tensor]":
-        return OrderedDict((s.key, self._view(self.momentum, s).detach().to("cpu", copy=True))
+        return OrderedDict((s.key, self._logical(self.momentum, s).detach().to("cpu", copy=True).contiguous())
                            for s in self.spec.segments)
 
     def load_momentum_state(self, sd: Dict[str, torch.Tensor]) -> None:
         for seg in self.spec.segments:
-            self._view(self.momentum, seg).copy_(sd[seg.key].to(self.device, torch.float32))
+            self._view(self.momentum, seg).zero_()
+            self._logical(self.momentum, seg).copy_(sd[seg.key].to(self.device, torch.float32))
 
     def as_module(self) -> MLP:
-        m = MLP(self.spec.sizes)
+        m = MLP(self.spec.logical_sizes)
         m.load_state_dict(self.state_dict())
         return m
 

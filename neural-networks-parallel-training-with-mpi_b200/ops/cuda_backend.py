@@ -84,7 +84,8 @@ class GemmCompute:
             raise ValueError("the tensor-core path trains in bf16 (use --dtype bf16)")
         for s in spec.sizes[:-1]:
             if s % 8:
-                raise ValueError(f"tensor-core path needs feature / hidden sizes that are multiples of 8 (got {s})")
+                raise ValueError(f"tensor-core path needs physical widths that are multiples of 8 (got {s}); "
+                                 "build the spec with MLPSpec(sizes, pad_to=8)")
         self.nout = spec.sizes[-1]
         if self.nout > 4 and self.nout % 8:
             raise ValueError("n_outputs must be <= 4 (fused GEMV head) or a multiple of 8 (GEMM head)")
@@ -119,6 +120,11 @@ class GemmCompute:
         self.gemm_max_ctas = 0
 
     def prepare_batch(self, x, y):
+        k_phys = self.spec.sizes[0]
+        if x.shape[1] != k_phys:                       # padded input width: zero columns on the right
+            xb = torch.zeros(x.shape[0], k_phys, dtype=torch.bfloat16, device=x.device)
+            xb[:, :x.shape[1]].copy_(x)
+            return xb, y.to(torch.float32).contiguous()
         xb = torch.empty(x.shape, dtype=torch.bfloat16, device=x.device)
         if x.numel():
             if x.dtype == torch.bfloat16:
@@ -494,6 +500,10 @@ class CudaRuntime:
         spec: MLPSpec = trainer.spec
         self.comm, self.cfg = comm, cfg
         tiny = is_tiny(spec) and cfg.dtype == "fp32"
+        if not tiny and any(s % 8 for s in spec.sizes[:-1]):
+            # tensor-core path: rows must be whole 16-byte vectors -> pad widths to multiples of 8
+            spec = MLPSpec(spec.logical_sizes, pad_to=8)
+            trainer.spec = spec
         if not tiny and cfg.dtype != "bf16":
             raise ValueError("models beyond the fused SIMT kernel's size train on the tensor-core path: "
                              "pass --dtype bf16")

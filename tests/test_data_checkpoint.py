@@ -127,3 +127,34 @@ def test_validation_and_jsonl(tmp_path):
     import json
     recs = [json.loads(l) for l in open(log)]
     assert len(recs) == 2 and "samples_per_s" in recs[0] and "global_loss" in recs[0]
+
+
+def test_padded_spec_keeps_logical_state_dict_and_zero_padding():
+    """Widths that are not multiples of 8 are padded inside the flat buffers (tensor-core path); the
+    padding is invisible in state_dict and mathematically inert."""
+    from b200dp.ops import reference as ref_ops
+    spec = MLPSpec([5, 10, 3, 1], pad_to=8)
+    assert spec.sizes == (8, 16, 8, 1) and spec.logical_sizes == (5, 10, 3, 1)
+    assert spec.num_params == 5 * 10 + 10 + 10 * 3 + 3 + 3 + 1
+    flat = FlatMLP(spec, "cpu")
+    flat.init_like_reference(0)
+    sd = flat.state_dict()
+    assert [tuple(v.shape) for v in sd.values()] == [(10, 5), (10,), (3, 10), (3,), (1, 3), (1,)]
+    w0 = flat.weight(0)
+    assert w0.shape == (16, 8) and float(w0[10:].abs().sum()) == 0 and float(w0[:, 5:].abs().sum()) == 0
+    torch.manual_seed(0)
+    ref = MLP([5, 10, 3, 1])
+    x = torch.randn(7, 5)
+    xp = torch.zeros(7, 8)
+    xp[:, :5] = x
+    torch.testing.assert_close(ref_ops.mlp_forward(flat, xp), ref(x))
+    # one training step leaves the padding at zero and matches the unpadded model
+    y = torch.randn(7, 1)
+    ref_ops.mlp_loss_and_grads(flat, xp, y)
+    g0 = flat.weight(0, flat.grads)
+    assert float(g0[10:].abs().sum()) == 0 and float(g0[:, 5:].abs().sum()) == 0
+    torch.nn.functional.mse_loss(ref(x), y).backward()
+    torch.testing.assert_close(g0[:10, :5], ref.layers[0].weight.grad)
+    flat2 = FlatMLP(MLPSpec([5, 10, 3, 1], pad_to=8), "cpu")
+    flat2.load_state_dict(sd)
+    assert flat2.fingerprint() == flat.fingerprint()

@@ -125,3 +125,35 @@ def test_host_fed_training_equals_resident_training():
     c = Trainer(TrainConfig(**kw), device=torch.device("cuda"))
     lc = c.fit_host_batches(iter([(a.shard.x.pin_memory(), yh)] * 2), 2)
     assert lc == la[:2]
+
+
+def test_tensor_core_path_with_unaligned_widths():
+    """hidden=100, 52 and 30 input features are padded to multiples of 8 inside the flat buffers."""
+    from b200dp.config import TrainConfig
+    from b200dp.engine import Trainer
+    cfg = TrainConfig(quiet=True, nepochs=0, hidden=[100, 52], n_features=30, n_samples=512, dtype="bf16",
+                      data_source="randn", data_dist="local", scale="none", lr=0.01, noise=0.1)
+    t = Trainer(cfg, device=torch.device("cuda"))
+    assert t.compute.name == "cuda-tcgen05" and t.spec.sizes == (32, 104, 56, 1)
+    m = t.flat.as_module().cuda()
+    for p in m.parameters():
+        p.data = p.data.bfloat16().float()
+    x32, y32 = t.shard.x.cuda(), t.shard.y.cuda()
+    ref_loss = torch.nn.functional.mse_loss(m(x32.bfloat16().float()), y32)
+    ref_loss.backward()
+    loss = t.compute.loss_and_grads(t.x, t.y)
+    torch.testing.assert_close(loss, ref_loss.detach(), rtol=2e-2, atol=1e-3)
+    sd_keys = list(t.state_dict().items())
+    assert [tuple(v.shape) for _, v in sd_keys] == [(100, 30), (100,), (52, 100), (52,), (1, 52), (1,)]
+    for seg, p in zip(t.spec.segments, m.parameters()):
+        got = t.flat._logical(t.flat.grads, seg).float()
+        scale = p.grad.abs().max().item() + 1e-12
+        assert (got - p.grad).abs().max().item() <= 5e-2 * scale, seg.key
+        full = t.flat._view(t.flat.grads, seg).float()
+        assert abs(float(full.abs().sum()) - float(got.abs().sum())) <= 1e-3 * float(got.abs().sum()) + 1e-6
+    first = float(loss.item())            # the loss tensor is a persistent device scalar: read it now
+    for _ in range(20):
+        last = t.step(t.x, t.y)
+    assert float(last.item()) < first
+    pred = t.predict(t.shard.x[:8])
+    assert pred.shape == (8, 1)
