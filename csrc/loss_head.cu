@@ -88,6 +88,7 @@ head_fwd_kernel(const __nv_bfloat16* __restrict__ H, long long ldh, const __nv_b
     float s[NOUT];
 #pragma unroll
     for (int o = 0; o < NOUT; ++o) s[o] = 0.0f;
+#pragma unroll 4
     for (int k = lane * 8; k < K; k += 256) {
       const uint4 hv = __ldg(reinterpret_cast<const uint4*>(h + k));
       const uint32_t hw[4] = {hv.x, hv.y, hv.z, hv.w};
@@ -152,6 +153,7 @@ head_bwd_kernel(const float* __restrict__ dy, const __nv_bfloat16* __restrict__ 
 #pragma unroll
   for (int o = 0; o < NOUT; ++o) bacc[o] = 0.0f;
 
+#pragma unroll 4
   for (int r = r_begin; r < r_end; ++r) {
     float g[NOUT];
 #pragma unroll
@@ -202,26 +204,50 @@ head_bwd_kernel(const float* __restrict__ dy, const __nv_bfloat16* __restrict__ 
   }
 }
 
-// out[j] = sum_s partials[s][j] (fixed order), fp32 or bf16 output; segment-aware copy so one
-// launch can scatter "[NOUT][K+1]" head partials into the separate weight / bias gradient slots.
-template <bool OUT_BF16>
-__global__ void reduce_partials_kernel(const float* __restrict__ partials, int strips, long long n, void* out) {
-  const long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (j >= n) return;
+// out[j] = sum_s partials[s][j], fp32 or bf16 output.  A block owns 64 columns; its 4 thread groups
+// each add every 4th strip (loads independent, unrolled), then the 4 group sums are added in group
+// order - a fixed summation tree, so the result is bit-reproducible.
+constexpr int kRedCols = 64;
+constexpr int kRedGroups = 4;
+
+__device__ __forceinline__ float strided_strip_sum(const float* __restrict__ partials, int strips, long long n,
+                                                   long long j, float (*sm)[kRedCols]) {
+  const int c = threadIdx.x % kRedCols, g = threadIdx.x / kRedCols;
   float s = 0.0f;
-  for (int t = 0; t < strips; ++t) s += partials[(long long)t * n + j];
+  if (j < n) {
+#pragma unroll 8
+    for (int t = g; t < strips; t += kRedGroups) s += partials[(long long)t * n + j];
+  }
+  sm[g][c] = s;
+  __syncthreads();
+  float tot = 0.0f;
+  if (g == 0) {
+#pragma unroll
+    for (int q = 0; q < kRedGroups; ++q) tot += sm[q][c];
+  }
+  return tot;
+}
+
+template <bool OUT_BF16>
+__global__ void __launch_bounds__(kRedCols * kRedGroups)
+reduce_partials_kernel(const float* __restrict__ partials, int strips, long long n, void* out) {
+  __shared__ float sm[kRedGroups][kRedCols];
+  const long long j = (long long)blockIdx.x * kRedCols + threadIdx.x % kRedCols;
+  const float s = strided_strip_sum(partials, strips, n, j, sm);
+  if (threadIdx.x >= kRedCols || j >= n) return;
   if (OUT_BF16) reinterpret_cast<__nv_bfloat16*>(out)[j] = __float2bfloat16_rn(s);
   else reinterpret_cast<float*>(out)[j] = s;
 }
 
+// same reduction; scatters the "[NOUT][K+1]" head partials into the weight / bias gradient slots
 template <bool OUT_BF16>
-__global__ void head_reduce_kernel(const float* __restrict__ partials, int strips, int nout, int K, void* dW,
-                                   void* db) {
+__global__ void __launch_bounds__(kRedCols * kRedGroups)
+head_reduce_kernel(const float* __restrict__ partials, int strips, int nout, int K, void* dW, void* db) {
+  __shared__ float sm[kRedGroups][kRedCols];
   const long long n = (long long)nout * (K + 1);
-  const long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (j >= n) return;
-  float s = 0.0f;
-  for (int t = 0; t < strips; ++t) s += partials[(long long)t * n + j];
+  const long long j = (long long)blockIdx.x * kRedCols + threadIdx.x % kRedCols;
+  const float s = strided_strip_sum(partials, strips, n, j, sm);
+  if (threadIdx.x >= kRedCols || j >= n) return;
   const int o = int(j / (K + 1)), k = int(j % (K + 1));
   void* dst = k < K ? dW : db;
   const long long idx = k < K ? (long long)o * K + k : o;
@@ -347,9 +373,9 @@ extern "C" int b200dp_head_bwd(const float* dy, const void* W, const void* H, lo
 #undef LAUNCH
   B200DP_CUDA_OK(cudaGetLastError());
   const long long n = (long long)nout * (K + 1);
-  const int rgrid = int((n + 255) / 256);
-  if (grads_bf16) head_reduce_kernel<true><<<rgrid, 256, 0, s>>>(partials, strips, nout, K, dW, db);
-  else head_reduce_kernel<false><<<rgrid, 256, 0, s>>>(partials, strips, nout, K, dW, db);
+  const int rgrid = int((n + kRedCols - 1) / kRedCols);
+  if (grads_bf16) head_reduce_kernel<true><<<rgrid, kRedCols * kRedGroups, 0, s>>>(partials, strips, nout, K, dW, db);
+  else head_reduce_kernel<false><<<rgrid, kRedCols * kRedGroups, 0, s>>>(partials, strips, nout, K, dW, db);
   B200DP_CUDA_OK(cudaGetLastError());
   return B200DP_OK;
 }
@@ -372,9 +398,9 @@ extern "C" int b200dp_colsum_bf16(const void* A, long long lda, int rows, int n,
   colsum_kernel<<<grid, 256, 0, s>>>(reinterpret_cast<const __nv_bfloat16*>(A), lda, rows, n, rows_per_strip,
                                      partials);
   B200DP_CUDA_OK(cudaGetLastError());
-  const int rgrid = (n + 255) / 256;
-  if (out_bf16) reduce_partials_kernel<true><<<rgrid, 256, 0, s>>>(partials, strips, n, out);
-  else reduce_partials_kernel<false><<<rgrid, 256, 0, s>>>(partials, strips, n, out);
+  const int rgrid = (n + kRedCols - 1) / kRedCols;
+  if (out_bf16) reduce_partials_kernel<true><<<rgrid, kRedCols * kRedGroups, 0, s>>>(partials, strips, n, out);
+  else reduce_partials_kernel<false><<<rgrid, kRedCols * kRedGroups, 0, s>>>(partials, strips, n, out);
   B200DP_CUDA_OK(cudaGetLastError());
   return B200DP_OK;
 }

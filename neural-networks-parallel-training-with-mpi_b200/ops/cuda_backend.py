@@ -457,6 +457,35 @@ class FusedSync(BucketedSync):
     def _run_bucket(self, b, lr, mu, stream):
         ar.launch(self.args, b.start, b.stop - b.start, lr, mu, False, stream=stream)
 
+    def calibrate(self, modes, iters: int = 4) -> str:
+        """Start-up pick between sync variants: times each on the largest bucket (device-timed, max
+        over ranks) and keeps the fastest - topology quirks (a 4-GPU subset of an 8-GPU NVSwitch
+        domain, a box without NVLS) then cannot leave a slow default in place.  Runs with lr = 0,
+        mu = 1 on the still-zero gradient buffer, so parameters and momentum are left bit-identical.
+        Every rank executes the same launch sequence and adopts the same answer."""
+        b = max(self.buckets, key=lambda k: k.stop - k.start)
+        n = b.stop - b.start
+        best, best_ms = self.name, float("inf")
+        for mode in modes:
+            self.args.mode = ar.MODES[mode]
+            for _ in range(2):
+                ar.launch(self.args, b.start, n, 0.0, 1.0, False)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.synchronize()
+            self.comm.barrier()
+            e0.record()
+            for _ in range(iters):
+                ar.launch(self.args, b.start, n, 0.0, 1.0, False)
+            e1.record()
+            torch.cuda.synchronize()
+            ms = max(self.comm.allgather(e0.elapsed_time(e1) / iters))
+            if ms < best_ms:
+                best, best_ms = mode, ms
+        self.args.mode = ar.MODES[best]
+        self.name = best
+        self.check_errors()
+        return best
+
     def check_errors(self) -> None:
         v = int(self.error_flag.item())
         if v:
@@ -523,8 +552,9 @@ class CudaRuntime:
         self.symm: Optional[SymmLayout] = None
         grads_bf16 = cfg.dtype == "bf16"
         if fused:
+            big = spec.flat_numel * 4 > 256 * 1024
             self.symm = SymmLayout(comm, dev, spec.flat_numel, grads_bf16, cfg.dtype == "bf16",
-                                   multicast=(sync_name == "fused_nvls"))
+                                   multicast=(sync_name == "fused_nvls" or (auto and big)))
             if sync_name == "fused_nvls" and self.symm.buf.mc_ptr is None:
                 if comm.rank == 0 and not auto:
                     print("b200dp: NVLS multicast is not available on this box - using fused_twoshot")
@@ -549,6 +579,8 @@ class CudaRuntime:
             self.sync = FusedSync(comm, weights, divisor, sync_name, self.flat, self.symm, self.buckets,
                                   overlap=overlap, max_blocks=0, timeout_ms=cfg.watchdog_ms)
             self.device_broadcast = self._device_broadcast
+            if auto and sync_name != "fused_oneshot" and self.symm.buf.mc_ptr is not None:
+                sync_name = self.sync.calibrate(("fused_twoshot", "fused_nvls"))
         elif sync_name == "allreduce":
             self.sync = NcclAllReduceSync(comm, weights, divisor, self.flat, self.buckets, overlap)
         elif sync_name == "gather_root":
