@@ -11,6 +11,7 @@ ranks.  Prints ONE JSON line on rank 0.
 --config deep            configs[3]: 4096 -> 16x8192 -> 1 (1.04 B parameters), bf16, 8192 rows per GPU.
 --config ref             configs[0-1]: the reference's own 2-3-1 MLP on make_regression(16, 2) (strong
                          scaling: 16 rows in total, as hard-coded at ref.py:72).
+--config ref_uneven      configs[1]: the same net on 17 rows (uneven shards, sample-weighted gradients).
 
 --impl ours (default)    this framework: kernel-only `value` (inputs resident on the device) and the
                          end-to-end number `e2e` through Trainer.fit_host_batches (pinned host batches,
@@ -40,6 +41,8 @@ CONFIGS = {
                  scaling="weak", name="deep MLP 4096-16x8192-1 (1.04B params)"),
     "ref": dict(n_features=2, hidden=[3], n_outputs=1, rows_total=16, dtype="fp32", scaling="strong",
                 name="reference MLP 2-3-1 on make_regression(16,2)"),
+    "ref_uneven": dict(n_features=2, hidden=[3], n_outputs=1, rows_total=17, dtype="fp32", scaling="strong",
+                       name="reference MLP 2-3-1 on make_regression(17,2): rows not a multiple of the world size"),
 }
 
 
@@ -109,8 +112,10 @@ def make_trainer(args, cfgd, rank, world):
     from b200dp.config import TrainConfig
     from b200dp.engine import Trainer
     from b200dp.parallel.comm import world_comm
-    if args.config == "ref":
-        cfg = TrainConfig(quiet=True, nepochs=0, sync=args.sync, data_dist="local")
+    if args.config in ("ref", "ref_uneven"):
+        cfg = TrainConfig(quiet=True, nepochs=0, sync=args.sync, data_dist="local",
+                          n_samples=cfgd["rows_total"],
+                          grad_weighting="samples" if args.config == "ref_uneven" else "uniform")
     else:
         rows = args.rows_per_gpu or cfgd["rows_per_gpu"]
         cfg = TrainConfig(quiet=True, nepochs=0, n_samples=rows * world, n_features=cfgd["n_features"],
@@ -131,7 +136,7 @@ def run_ours(args, rank, world):
     K, W = args.steps, max(args.warmup, 3)
 
     # ---- kernel-only: inputs resident on the device -------------------------------------------
-    graphed = (args.cuda_graph == "on" or (args.cuda_graph == "auto" and args.config == "ref")) \
+    graphed = (args.cuda_graph == "on" or (args.cuda_graph == "auto" and args.config.startswith("ref"))) \
         and t.capture_full_shard_step()
     step = t.graph_step if graphed else (lambda: t.step(t.x, t.y))
     # nvidia-smi needs ~100 ms to come up: start it before the warm-up and wait for its first line, so
@@ -200,7 +205,7 @@ def run_ours(args, rank, world):
         "config": {"model": cfgd["name"], "global_batch": global_batch, "seq_len": None,
                    "parallelism": f"dp{world}", "sync": getattr(t._runtime, "sync_name", t.sync.name),
                    "rows_per_gpu": rows_local, "params": spec.num_params, "cuda_graph": bool(graphed),
-                   "l2": "inputs+weights larger than L2 (no flush needed)" if args.config != "ref"
+                   "l2": "inputs+weights larger than L2 (no flush needed)" if not args.config.startswith("ref")
                    else "working set is 13 parameters: cache-resident by nature"},
         "clocks": {"sm_mhz": clocks.get("sm_mhz"), "sm_max_mhz": clocks.get("sm_max_mhz"),
                    "reasons": clocks.get("reasons", [])},
@@ -220,7 +225,7 @@ def run_torch(args, rank, world):
     cfgd = CONFIGS[args.config]
     dev = torch.device("cuda", torch.cuda.current_device())
     sizes = [cfgd["n_features"], *cfgd["hidden"], cfgd["n_outputs"]]
-    if args.config == "ref":
+    if args.config.startswith("ref"):
         rows_total = cfgd["rows_total"]
         rows = rows_total // world + (1 if rank < rows_total % world else 0)
         cdt = torch.float32
