@@ -80,9 +80,23 @@ inline int ew_grid(long long n) {
 
 using namespace b200dp;
 
+extern "C" int b200dp_sgd_momentum_ex(float* params, const void* grads, int grads_bf16, float* momentum,
+                                      void* shadow_bf16, long long n, float lr, float mu, float grad_scale,
+                                      int first_step, int max_blocks, void* stream);
+
 extern "C" int b200dp_sgd_momentum(float* params, const void* grads, int grads_bf16, float* momentum,
                                    void* shadow_bf16, long long n, float lr, float mu, float grad_scale,
                                    int first_step, void* stream) {
+  return b200dp_sgd_momentum_ex(params, grads, grads_bf16, momentum, shadow_bf16, n, lr, mu, grad_scale, first_step,
+                                0, stream);
+}
+
+// max_blocks > 0 caps the grid: an update that runs beside tensor-core GEMMs is deliberately held
+// below the full HBM rate so the GEMMs' TMA loads keep their latency (it only has to finish before
+// the layer's backward does).
+extern "C" int b200dp_sgd_momentum_ex(float* params, const void* grads, int grads_bf16, float* momentum,
+                                      void* shadow_bf16, long long n, float lr, float mu, float grad_scale,
+                                      int first_step, int max_blocks, void* stream) {
   B200DP_REQUIRE(params && grads && momentum, "sgd: null pointer");
   B200DP_REQUIRE(n % 4 == 0, "sgd: n must be a multiple of 4 (flat buffers are padded)");
   B200DP_REQUIRE(((uintptr_t)params & 15) == 0 && ((uintptr_t)momentum & 15) == 0 &&
@@ -90,7 +104,8 @@ extern "C" int b200dp_sgd_momentum(float* params, const void* grads, int grads_b
                  "sgd: buffers must be 16-byte aligned");
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   const long long n4 = n / 4;
-  const int grid = ew_grid(n4);
+  int grid = ew_grid(n4);
+  if (max_blocks > 0 && grid > max_blocks) grid = max_blocks;
   if (grads_bf16)
     sgd_kernel<true><<<grid, 256, 0, s>>>(params, grads, momentum, reinterpret_cast<__nv_bfloat16*>(shadow_bf16),
                                           n4, lr, mu, grad_scale, first_step);

@@ -128,6 +128,10 @@ int b200dp_colsum_bf16(const void* A, long long lda, int rows, int n, void* out,
  */
 int b200dp_sgd_momentum(float* params, const void* grads, int grads_bf16, float* momentum, void* shadow_bf16,
                         long long n, float lr, float mu, float grad_scale, int first_step, void* stream);
+/* Same with a cap on the grid (0 = none): keeps an update that overlaps GEMMs below the full HBM rate. */
+int b200dp_sgd_momentum_ex(float* params, const void* grads, int grads_bf16, float* momentum, void* shadow_bf16,
+                           long long n, float lr, float mu, float grad_scale, int first_step, int max_blocks,
+                           void* stream);
 int b200dp_cast_f32_bf16(const float* src, void* dst, long long n, void* stream);
 /* Mini-batch assembly on the device: dst[r,:] = src[idx[r],:], rows of `row_bytes` bytes (multiple of
  * 16; idx is int64 on the device).  Stands in for the DataLoader's shuffle + collate when the batch

@@ -383,12 +383,14 @@ class BucketedSync(GradSync):
 class CudaLocalSync(BucketedSync):
     """World of one: the fused SGD kernel per bucket (HBM-bound; hidden under backward's GEMMs)."""
     name = "local"
+    update_blocks = int(__import__("os").environ.get("B200DP_UPDATE_BLOCKS", "0"))
 
     def _run_bucket(self, b, lr, mu, stream):
         f = self.flat
         sl = slice(b.start, b.stop)
         K.sgd_momentum(f.params[sl], f.grads[sl], f.momentum[sl], f.shadow[sl] if f.shadow is not None else None,
-                       lr, mu, first_step=False, grad_scale=1.0, stream=stream)
+                       lr, mu, first_step=False, grad_scale=1.0, stream=stream,
+                       max_blocks=self.update_blocks if self.comm_stream is not None else 0)
 
 
 class NcclAllReduceSync(BucketedSync):

@@ -28,6 +28,8 @@ _lib.register("b200dp_head_bwd", [c_void_p, c_void_p, c_void_p, c_ll, c_int, c_i
 _lib.register("b200dp_colsum_bf16", [c_void_p, c_ll, c_int, c_int, c_void_p, c_int, c_void_p, c_ll, c_void_p])
 _lib.register("b200dp_sgd_momentum", [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_ll, c_float, c_float,
                                       c_float, c_int, c_void_p])
+_lib.register("b200dp_sgd_momentum_ex", [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_ll, c_float, c_float,
+                                         c_float, c_int, c_int, c_void_p])
 _lib.register("b200dp_cast_f32_bf16", [c_void_p, c_void_p, c_ll, c_void_p])
 _lib.register("b200dp_gather_rows", [c_void_p, c_ll, c_void_p, c_int, c_ll, c_void_p, c_void_p])
 
@@ -136,10 +138,10 @@ def colsum(A, out, scratch_buf, stream=None):
 
 
 # ------------------------------------------------------------------------------------------ optim
-def sgd_momentum(params, grads, momentum, shadow, lr, mu, first_step, grad_scale=1.0, stream=None):
-    _lib.check(L().b200dp_sgd_momentum(params.data_ptr(), grads.data_ptr(), int(grads.dtype == torch.bfloat16),
-                                       momentum.data_ptr(), _lib.ptr(shadow), params.numel(), lr, mu,
-                                       grad_scale, int(first_step), _lib.stream_ptr(stream)))
+def sgd_momentum(params, grads, momentum, shadow, lr, mu, first_step, grad_scale=1.0, stream=None, max_blocks=0):
+    _lib.check(L().b200dp_sgd_momentum_ex(params.data_ptr(), grads.data_ptr(), int(grads.dtype == torch.bfloat16),
+                                          momentum.data_ptr(), _lib.ptr(shadow), params.numel(), lr, mu,
+                                          grad_scale, int(first_step), max_blocks, _lib.stream_ptr(stream)))
     _lib.count()
 
 
