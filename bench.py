@@ -141,7 +141,7 @@ def run_ours(args, rank, world):
     step = t.graph_step if graphed else (lambda: t.step(t.x, t.y))
     # nvidia-smi needs ~100 ms to come up: start it before the warm-up and wait for its first line, so
     # that it is sampling (every 50 ms) while the timed region runs
-    sampler = ClockSampler(torch.cuda.current_device(), period_ms=50).start() if rank == 0 else None
+    sampler = ClockSampler(torch.cuda.current_device(), period_ms=100).start() if rank == 0 else None
     for _ in range(W):
         step()
     torch.cuda.synchronize()

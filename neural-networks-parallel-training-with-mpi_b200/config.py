@@ -52,7 +52,8 @@ class TrainConfig:
     backend: str = "auto"
     sync: str = "auto"
     grad_weighting: str = "uniform"       # Q6
-    bucket_mb: float = 0.0                # 0 = one bucket per layer
+    bucket_mb: float = 0.0                # 0 = one bucket per layer (large layers in <= 3 row chunks)
+    calibrate_sync: bool = False          # sync=auto: time two-shot vs NVLS at start-up and keep the faster
     overlap: bool = True
     cuda_graph: bool = False
     # --- aux subsystems ---
@@ -139,6 +140,8 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--sync", choices=SYNC_MODES, default=d.sync)
     p.add_argument("--grad-weighting", choices=GRAD_WEIGHTING, default=d.grad_weighting)
     p.add_argument("--bucket-mb", type=float, default=d.bucket_mb)
+    p.add_argument("--calibrate-sync", action="store_true",
+                   help="with --sync auto: time the two-shot and NVLS kernels at start-up, keep the faster")
     p.add_argument("--no-overlap", dest="overlap", action="store_false")
     p.add_argument("--cuda-graph", action="store_true")
     # aux

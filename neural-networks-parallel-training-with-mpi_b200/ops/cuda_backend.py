@@ -468,6 +468,8 @@ class FusedSync(BucketedSync):
         b = max(self.buckets, key=lambda k: k.stop - k.start)
         n = b.stop - b.start
         best, best_ms = self.name, float("inf")
+        torch.cuda.synchronize()
+        self.comm.barrier()                 # no rank may start spinning long before its peers arrive
         for mode in modes:
             self.args.mode = ar.MODES[mode]
             for _ in range(2):
@@ -554,9 +556,9 @@ class CudaRuntime:
         self.symm: Optional[SymmLayout] = None
         grads_bf16 = cfg.dtype == "bf16"
         if fused:
-            big = spec.flat_numel * 4 > 256 * 1024
+            calibrate = auto and cfg.calibrate_sync and spec.flat_numel * 4 > 256 * 1024
             self.symm = SymmLayout(comm, dev, spec.flat_numel, grads_bf16, cfg.dtype == "bf16",
-                                   multicast=(sync_name == "fused_nvls" or (auto and big)))
+                                   multicast=(sync_name == "fused_nvls" or calibrate))
             if sync_name == "fused_nvls" and self.symm.buf.mc_ptr is None:
                 if comm.rank == 0 and not auto:
                     print("b200dp: NVLS multicast is not available on this box - using fused_twoshot")
@@ -581,7 +583,7 @@ class CudaRuntime:
             self.sync = FusedSync(comm, weights, divisor, sync_name, self.flat, self.symm, self.buckets,
                                   overlap=overlap, max_blocks=0, timeout_ms=cfg.watchdog_ms)
             self.device_broadcast = self._device_broadcast
-            if auto and sync_name != "fused_oneshot" and self.symm.buf.mc_ptr is not None:
+            if calibrate and self.symm.buf.mc_ptr is not None:
                 sync_name = self.sync.calibrate(("fused_twoshot", "fused_nvls"))
         elif sync_name == "allreduce":
             self.sync = NcclAllReduceSync(comm, weights, divisor, self.flat, self.buckets, overlap)
