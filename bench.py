@@ -142,6 +142,8 @@ def run_ours(args, rank, world):
     # nvidia-smi needs ~100 ms to come up: start it before the warm-up and wait for its first line, so
     # that it is sampling (every 50 ms) while the timed region runs
     sampler = ClockSampler(torch.cuda.current_device(), period_ms=100).start() if rank == 0 else None
+    torch.cuda.synchronize()
+    barrier(world)                       # ranks enter the first cross-GPU kernel together
     for _ in range(W):
         step()
     torch.cuda.synchronize()
@@ -179,6 +181,8 @@ def run_ours(args, rank, world):
             while True:
                 yield xh[i & 1], yh[i & 1]
                 i += 1
+        torch.cuda.synchronize()
+        barrier(world)                   # pinning the host batches takes a rank-dependent time
         t.fit_host_batches(batches(), W)
         torch.cuda.synchronize()
         barrier(world)

@@ -95,6 +95,11 @@ class Trainer:
         self.plan = BatchPlan(self.shard.rows, batch, cfg.shuffle, seed=cfg.seed + 1 + self.rank)
         self.x, self.y = self.compute.prepare_batch(self.shard.x.to(self.device),
                                                     self.shard.y.to(self.device))
+        if self.world > 1 and self.device.type == "cuda":
+            # the first fused sync kernel spins on its peers with a bounded budget (watchdog): start the
+            # ranks together so set-up skew (data generation, allocation) cannot eat into that budget
+            torch.cuda.synchronize()
+            self.comm.barrier()
 
     # ------------------------------------------------------------------ init
     def _replicate_initial_state(self):
