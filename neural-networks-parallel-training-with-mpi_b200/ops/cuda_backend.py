@@ -19,7 +19,7 @@ No PyTorch op runs inside the step; torch only owns memory and streams.
 from __future__ import annotations
 
 from dataclasses import dataclass
-from typing import Callable, List, Optional, Tuple
+from typing import Callable, List, Optional
 
 import torch
 

@@ -19,7 +19,7 @@ and leaves all replicas bitwise identical.
 """
 from __future__ import annotations
 
-from typing import List, Sequence
+from typing import Sequence
 
 import torch
 

@@ -4,7 +4,7 @@ from __future__ import annotations
 import json
 import sys
 import time
-from typing import Any, Dict, Optional
+from typing import Any, Optional
 
 
 def epoch_banner(epoch: int) -> str:

@@ -3,7 +3,6 @@
 discussion uses.  python tools/ncu_summary.py gpurun_out/prof.ncu-rep > profiles/xyz.md"""
 import csv
 import io
-import json
 import os
 import subprocess
 import sys
