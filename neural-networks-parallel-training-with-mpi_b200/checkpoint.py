@@ -47,7 +47,7 @@ def save_checkpoint(path: str, flat, epoch: int, config: Dict[str, Any], extra: 
 
 
 def load_checkpoint(path: str, flat, strict_sizes: bool = True) -> Dict[str, Any]:
-    payload = torch.load(path, map_location="cpu", weights_only=False)
+    payload = torch.load(path, map_location="cpu", weights_only=True)   # tensors and plain containers only
     if isinstance(payload, dict) and "model" not in payload:
         payload = {"model": payload}                     # a bare state_dict (e.g. from the reference's MLP)
     if strict_sizes and "sizes" in payload and tuple(payload["sizes"]) != tuple(flat.spec.logical_sizes):

@@ -631,14 +631,13 @@ class CudaRuntime:
         torch.cuda.synchronize()
 
     def close(self) -> None:
-        if isinstance(self.sync, FusedSync):
-            try:
+        try:
+            if isinstance(self.sync, FusedSync):
                 self.sync.check_errors()
-            finally:
-                pass
-        if self.symm is not None:
-            self.symm.buf.close()
-            self.symm = None
+        finally:
+            if self.symm is not None:
+                self.symm.buf.close()
+                self.symm = None
 
 
 def build_cuda_runtime(trainer) -> CudaRuntime:
