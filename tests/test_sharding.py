@@ -44,3 +44,19 @@ def test_grad_weights():
 def test_bad_world():
     with pytest.raises(ValueError):
         shard_counts(4, 0)
+
+
+from hypothesis import given, settings, strategies as st
+
+
+@settings(max_examples=200, deadline=None)
+@given(rows=st.integers(0, 10**7), world=st.integers(1, 512))
+def test_shard_properties(rows, world):
+    c = shard_counts(rows, world)
+    d = shard_displs(c)
+    assert sum(c) == rows and len(c) == world and max(c) - min(c) <= 1
+    assert c == sorted(c, reverse=True)                      # the extra rows go to the first ranks
+    assert all(d[i + 1] == d[i] + c[i] for i in range(world - 1))
+    ws = grad_weights(rows, world, "samples") if rows else None
+    if ws:
+        assert abs(sum(ws) - 1.0) < 1e-9
