@@ -52,3 +52,23 @@ def test_mpiexec_style_env_single_rank():
                        capture_output=True, text=True, env=env, cwd=ROOT, timeout=300)
     assert r.returncode == 0, r.stderr[-2000:]
     assert _losses(r.stdout, 0) == pytest.approx([2530.8320], rel=2e-6)
+
+
+@pytest.mark.timeout(600)
+def test_mpiexec_style_launch_two_ranks():
+    """What `mpiexec -n 2 python dataParallelTraining_NN_MPI.py` does (README:12): every process gets
+    only Open MPI's rank variables; the trainer must find its rank and peers from them."""
+    port = _free_port()
+    procs = []
+    for r in range(2):
+        env = dict(os.environ, OMPI_COMM_WORLD_RANK=str(r), OMPI_COMM_WORLD_SIZE="2",
+                   OMPI_COMM_WORLD_LOCAL_RANK=str(r), MASTER_PORT=str(port), CUDA_VISIBLE_DEVICES="",
+                   OMP_NUM_THREADS="1")
+        for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK"):
+            env.pop(k, None)
+        procs.append(subprocess.Popen([sys.executable, os.path.join(ROOT, "dataParallelTraining_NN_MPI.py")],
+                                      stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, env=env, cwd=ROOT))
+    outs = [p.communicate(timeout=500) for p in procs]
+    assert all(p.returncode == 0 for p in procs), [o[1][-1500:] for o in outs]
+    assert _losses(outs[0][0], 0) == pytest.approx([2230.0781, 2227.2244, 2221.5251], rel=2e-6)
+    assert _losses(outs[1][0], 1) == pytest.approx([2835.1191, 2831.0088, 2822.7883], rel=2e-6)
