@@ -165,6 +165,10 @@ class GemmCompute:
                     self.bucket_hook(l)
             return self.loss
         L, flat = self.L, self.flat
+        # every side-stream event of the previous step completed before that step ended (the streams are
+        # joined in sync_and_step); never wait on an event from before this step (or from before a
+        # CUDA-graph capture began)
+        self._colsum_pending = [False, False]
         h = self.forward_hidden(x)
         last = L - 1
         # ---- head forward + loss + dY, head backward ----

@@ -157,3 +157,17 @@ def test_tensor_core_path_with_unaligned_widths():
     assert float(last.item()) < first
     pred = t.predict(t.shard.x[:8])
     assert pred.shape == (8, 1)
+
+
+def test_cuda_graph_on_the_tensor_core_path_with_two_streams():
+    """Graph capture of a step that forks to the side stream (bucketed update, column sums) and joins."""
+    from b200dp.config import TrainConfig
+    from b200dp.engine import Trainer
+    kw = dict(quiet=True, nepochs=4, hidden=[256, 128, 64], n_features=64, n_samples=2048, dtype="bf16",
+              data_source="randn", data_dist="local", scale="none", lr=0.01, noise=0.1)
+    g = Trainer(TrainConfig(**kw, cuda_graph=True), device=torch.device("cuda"))
+    e = Trainer(TrainConfig(**kw), device=torch.device("cuda"))
+    lg = [h["loss"] for h in g.train()]
+    le = [h["loss"] for h in e.train()]
+    assert g._graph is not None and g._graph_launches > 5
+    assert lg == le and g.flat.fingerprint() == e.flat.fingerprint()
