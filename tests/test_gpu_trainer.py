@@ -171,3 +171,18 @@ def test_cuda_graph_on_the_tensor_core_path_with_two_streams():
     le = [h["loss"] for h in e.train()]
     assert g._graph is not None and g._graph_launches > 5
     assert lg == le and g.flat.fingerprint() == e.flat.fingerprint()
+
+
+def test_row_chunked_wgrad_and_buckets_are_bitwise_neutral():
+    """A small bucket limit forces the first layer's weight into two row chunks (two wgrad GEMMs, two
+    update launches); the result must be bit-identical to the unchunked schedule."""
+    from b200dp.config import TrainConfig
+    from b200dp.engine import Trainer
+    kw = dict(quiet=True, nepochs=3, hidden=[2048, 64], n_features=4096, n_samples=1024, dtype="bf16",
+              data_source="randn", data_dist="local", scale="none", lr=0.01, noise=0.1)
+    a = Trainer(TrainConfig(**kw, bucket_mb=4.0), device=torch.device("cuda"))
+    b = Trainer(TrainConfig(**kw, bucket_mb=1000.0), device=torch.device("cuda"))
+    assert len(a._runtime.sync.chunks_of[0]) == 2 and len(b._runtime.sync.chunks_of[0]) == 1
+    la = [h["loss"] for h in a.train()]
+    lb = [h["loss"] for h in b.train()]
+    assert la == lb and a.flat.fingerprint() == b.flat.fingerprint()
