@@ -158,3 +158,41 @@ def test_padded_spec_keeps_logical_state_dict_and_zero_padding():
     flat2 = FlatMLP(MLPSpec([5, 10, 3, 1], pad_to=8), "cpu")
     flat2.load_state_dict(sd)
     assert flat2.fingerprint() == flat.fingerprint()
+
+
+def test_two_rank_resume_is_exact_and_only_rank0_writes(tmp_path):
+    path = str(tmp_path / "ck2.pt")
+
+    def full(comm):
+        t = Trainer(TrainConfig(quiet=True, nepochs=6), comm)
+        t.train()
+        return t.flat.fingerprint(), [h["loss"] for h in t.history]
+
+    def first_half(comm):
+        t = Trainer(TrainConfig(quiet=True, nepochs=3, checkpoint=path), comm)
+        t.train()
+        return t.flat.fingerprint()
+
+    def second_half(comm):
+        t = Trainer(TrainConfig(quiet=True, nepochs=6, resume=path), comm)
+        assert t.start_epoch == 3
+        t.train()
+        return t.flat.fingerprint(), [h["loss"] for h in t.history]
+
+    want = run_threads(2, full)
+    run_threads(2, first_half)
+    got = run_threads(2, second_half)
+    for r in range(2):
+        assert got[r][0] == want[r][0]
+        assert got[r][1] == want[r][1][3:]
+
+
+def test_global_loss_is_the_sample_weighted_mean():
+    def fn(comm):
+        t = Trainer(TrainConfig(quiet=True, nepochs=1, global_loss=True, n_samples=17, data_dist="local"), comm)
+        h = t.train()
+        return h[0]["loss"], t.shard.rows, h[0]["global_loss"]
+
+    res = run_threads(3, fn)
+    want = sum(l * n for l, n, _ in res) / sum(n for _, n, _ in res)
+    assert all(abs(g - want) < 1e-9 * abs(want) for _, _, g in res)
