@@ -51,6 +51,7 @@ struct SyncArgs {
   float lr, mu;
   int first;
   long long n;          // elements in this bucket
+  long long tail_from;  // elements [tail_from, n) also get their fp32 master written into every peer (modes 1/2)
   int push_master;
   int mode;             // 0 one-shot, 1 two-shot, 2 nvls
   unsigned long long timeout_ns;
@@ -61,9 +62,11 @@ struct SyncArgs {
 };
 
 // ---- cross-GPU barrier for one block index -----------------------------------------------------
-__device__ __forceinline__ void peer_barrier(const SyncArgs& a, int block, uint32_t target) {
+// Returns false (to every thread of the block) when a peer did not arrive within the time budget.
+__device__ __forceinline__ bool peer_barrier(const SyncArgs& a, int block, uint32_t target) {
   __syncthreads();
   const int t = threadIdx.x;
+  int timed_out = 0;
   if (t < a.world) {
     red_release_sys_add(a.flags[t] + block * B200DP_MAX_RANKS + a.rank, 1u);
     const uint32_t* mine = a.flags[a.rank] + block * B200DP_MAX_RANKS + t;
@@ -75,12 +78,13 @@ __device__ __forceinline__ void peer_barrier(const SyncArgs& a, int block, uint3
         if (t0 == 0) t0 = now;
         else if (a.timeout_ns && now - t0 > a.timeout_ns) {
           atomicExch(a.error_flag, 1u + uint32_t(t));      // which peer never arrived
+          timed_out = 1;
           break;
         }
       }
     }
   }
-  __syncthreads();
+  return __syncthreads_or(timed_out) == 0;
 }
 
 template <typename G> struct Vec;
@@ -197,7 +201,10 @@ template <typename G, int WR, int U>
 __device__ void sync_body(const SyncArgs& a, int block, int nblocks) {
   constexpr int VN = Vec<G>::N;
   const uint32_t epoch = a.epochs[block];
-  peer_barrier(a, block, epoch + 1);               // every rank's gradients for this bucket are final
+  // every rank's gradients for this bucket are final.  A peer that never shows up (dead process,
+  // diverged launch sequence) must not be averaged in from stale memory: leave parameters, momentum
+  // and the epoch counter untouched; the host reads error_flag and raises.
+  if (!peer_barrier(a, block, epoch + 1)) return;
 
   const long long units = a.n / VN;
   long long u_lo = 0, u_hi = units;
@@ -236,18 +243,21 @@ __device__ void sync_body(const SyncArgs& a, int block, int nblocks) {
       float p[VN];
       sgd_vec<VN>(a, i, g[k], p);
       store_master<VN>(a.params[a.rank] + i, p);
+      // fp32 values that kernels read straight from the master buffer (the biases: they sit at the end
+      // of a layer's bucket) must be identical on every rank, not only on the owner of their slice
+      const bool push_fp32 = a.push_master || i >= a.tail_from;
       if (a.mode == 0) {
         if (has_shadow) store_shadow<VN>(a.shadow[a.rank] + i, p);
       } else if (a.mode == 1) {
 #pragma unroll
         for (int r = 0; r < WR; ++r) {
           if (r < a.world) {
-            if (a.push_master && r != a.rank) store_master<VN>(a.params[r] + i, p);
+            if (push_fp32 && r != a.rank) store_master<VN>(a.params[r] + i, p);
             if (has_shadow) store_shadow<VN>(a.shadow[r] + i, p);
           }
         }
       } else {
-        if (a.push_master) {
+        if (push_fp32) {
 #pragma unroll
           for (int j = 0; j < VN; j += 4)
             asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(a.mc_params + i + j),
@@ -267,7 +277,7 @@ __device__ void sync_body(const SyncArgs& a, int block, int nblocks) {
     }
   }
   // all peers finished reading my gradients and every pushed parameter has landed
-  peer_barrier(a, block, epoch + 2);
+  if (!peer_barrier(a, block, epoch + 2)) return;
   if (threadIdx.x == 0) a.epochs[block] = epoch + 2;
 }
 
@@ -297,7 +307,7 @@ const void* pick_kernel(int world, bool emulated) {
 // ---- standalone barrier and broadcast ------------------------------------------------------------
 __global__ void barrier_kernel(const __grid_constant__ SyncArgs a) {
   const uint32_t epoch = a.epochs[blockIdx.x];
-  peer_barrier(a, blockIdx.x, epoch + 1);
+  if (!peer_barrier(a, blockIdx.x, epoch + 1)) return;
   if (threadIdx.x == 0) a.epochs[blockIdx.x] = epoch + 1;
 }
 
@@ -306,7 +316,7 @@ __global__ void barrier_kernel(const __grid_constant__ SyncArgs a) {
 __global__ void __launch_bounds__(kSyncThreads)
 broadcast_kernel(const __grid_constant__ SyncArgs a, int root, long long n16) {  // 256 threads
   const uint32_t epoch = a.epochs[blockIdx.x];
-  peer_barrier(a, blockIdx.x, epoch + 1);
+  if (!peer_barrier(a, blockIdx.x, epoch + 1)) return;
   if (a.rank != root) {
     const uint4* src = reinterpret_cast<const uint4*>(a.params[root]);
     uint4* dst = reinterpret_cast<uint4*>(a.params[a.rank]);
@@ -314,7 +324,7 @@ broadcast_kernel(const __grid_constant__ SyncArgs a, int root, long long n16) { 
          i += (long long)gridDim.x * blockDim.x)
       dst[i] = src[i];
   }
-  peer_barrier(a, blockIdx.x, epoch + 2);
+  if (!peer_barrier(a, blockIdx.x, epoch + 2)) return;
   if (threadIdx.x == 0) a.epochs[blockIdx.x] = epoch + 2;
 }
 
@@ -346,14 +356,27 @@ int fill_args(const b200dp_sync_args* in, SyncArgs* a) {
   a->epochs = in->epochs; a->error_flag = in->error_flag;
   a->div = in->div; a->lr = in->lr; a->mu = in->mu; a->first = in->first_step;
   a->n = in->n; a->push_master = in->push_master; a->mode = in->mode;
+  B200DP_REQUIRE(in->replicate_tail >= 0 && in->replicate_tail <= in->n && in->replicate_tail % vn == 0,
+                 "sync: replicate_tail must be a multiple of %d within the bucket", vn);
+  a->tail_from = in->n - in->replicate_tail;
   a->timeout_ns = in->timeout_ms > 0 ? (unsigned long long)in->timeout_ms * 1000000ull : 0ull;
   if (in->mode == 2) {
+    // the switch adds the ranks' values as they are: per-rank weights cannot be applied on the way.
+    // Callers with non-uniform weights pre-scale their gradients (the loss kernels take a grad_scale)
+    // and pass equal weights here.
+    for (int r = 1; r < in->world; ++r)
+      B200DP_REQUIRE(in->weights[r] == in->weights[0],
+                     "sync: NVLS mode sums in the switch and needs equal per-rank weights (rank %d has %g, rank 0 %g); "
+                     "pre-scale the gradients or use mode 1", r, double(in->weights[r]), double(in->weights[0]));
+    B200DP_REQUIRE(in->weights[0] != 0.0f, "sync: NVLS mode needs a non-zero common weight");
+    a->div = in->div / in->weights[0];
     B200DP_REQUIRE(in->mc_grads != nullptr, "sync: NVLS mode needs the multicast gradient address");
     a->mc_grads = reinterpret_cast<const char*>(in->mc_grads) + goff;
     a->mc_shadow = in->mc_shadow ? reinterpret_cast<__nv_bfloat16*>(in->mc_shadow) + in->offset : nullptr;
     a->mc_params = in->mc_params ? in->mc_params + in->offset : nullptr;
     B200DP_REQUIRE(!a->shadow[in->rank] || a->mc_shadow, "sync: NVLS mode needs the multicast shadow address");
-    B200DP_REQUIRE(!in->push_master || a->mc_params, "sync: NVLS push_master needs the multicast param address");
+    B200DP_REQUIRE(!(in->push_master || in->replicate_tail > 0) || a->mc_params,
+                   "sync: NVLS push_master / replicate_tail need the multicast param address");
   }
   return B200DP_OK;
 }
@@ -415,7 +438,7 @@ extern "C" int b200dp_allreduce_sgd_emulated(const b200dp_sync_args* per_rank, i
 
 extern "C" int b200dp_peer_barrier(const b200dp_sync_args* in, void* stream) {
   b200dp_sync_args tmp = *in;
-  tmp.n = 8; tmp.mode = 0;
+  tmp.n = 8; tmp.mode = 0; tmp.replicate_tail = 0;
   SyncArgs a;
   // the barrier needs only rank/world/flags/epochs; reuse the validation with dummy data pointers
   for (int r = 0; r < tmp.world; ++r) {
@@ -435,7 +458,7 @@ extern "C" int b200dp_broadcast(const b200dp_sync_args* in, int root, long long 
   B200DP_REQUIRE(in && root >= 0 && root < in->world, "broadcast: bad root");
   B200DP_REQUIRE(bytes > 0 && bytes % 16 == 0, "broadcast: size must be a positive multiple of 16 bytes");
   b200dp_sync_args tmp = *in;
-  tmp.n = 8; tmp.mode = 0; tmp.offset = 0;
+  tmp.n = 8; tmp.mode = 0; tmp.offset = 0; tmp.replicate_tail = 0;
   for (int r = 0; r < tmp.world; ++r)
     if (!tmp.grads[r]) tmp.grads[r] = tmp.params[r];
   if (!tmp.momentum) tmp.momentum = reinterpret_cast<float*>(tmp.epochs);

@@ -2,8 +2,8 @@
 // 256x256 output tile.  Each CTA stages its own 128 rows of A and HALF of the B tile (128 of the 256
 // columns); the pair's tensor cores read both halves, so per-SM shared-memory and L2->SM traffic
 // drop by a third (32 KB instead of 48 KB per 64-deep k-block) and the freed shared memory buys a
-// 6-stage TMA ring instead of 4.  Same math, epilogues and operand layouts as gemm_tcgen05.cu
-// (forward / dgrad / wgrad of ref.py:42-44,170,176 without transposed copies).
+// 6-stage TMA ring instead of 4.  Same math, epilogue (gemm_common.cuh) and operand layouts as
+// gemm_tcgen05.cu (forward / dgrad / wgrad of ref.py:42-44,170,176 without transposed copies).
 //
 // Protocol differences to the single-CTA kernel:
 //   * cluster of 2 CTAs; CTA rank 0 (the leader) issues every MMA for the pair;
@@ -12,46 +12,45 @@
 //     CTAs; the peer's epilogue warps arrive remotely on the leader's "accumulator drained" barrier;
 //   * TMEM is allocated/freed with cta_group::2 by the same warp of both CTAs, bracketed by cluster
 //     barriers so neither CTA exits while its partner can still touch its shared memory or TMEM.
-#include "common.cuh"
+//
+// Tail wave: T tiles over P pairs leave a last wave of T mod P tiles.  When that remainder would
+// keep at most half of the pairs busy (a 4096x4096 wgrad: 256 tiles = 3 x 74 + 34), its tiles are
+// computed as two independent 256x128 half tiles each (UMMA N = 128), so the last wave costs half
+// a tile time instead of a whole one.  Half tiles need no workspace, no inter-CTA dependency and
+// sum in the same order as whole tiles: results are bit-identical with and without the split.
+#include "gemm_common.cuh"
 
 namespace b200dp {
 namespace {
 
-constexpr int BM = 128;        // rows per CTA (UMMA M = 256 per pair)
+using T = __nv_bfloat16;
+constexpr int BM = kGemmBM;    // rows per CTA (UMMA M = 256 per pair)
 constexpr int BN = 256;        // columns per pair
 constexpr int BNH = 128;       // B columns staged by each CTA
-constexpr int BK = 64;
-constexpr int UMMA_K = 16;
+constexpr int BK = Elem<T>::BK;
+constexpr int UMMA_K = Elem<T>::UMMA_K;
 constexpr int kStages = 6;
-constexpr int kThreads = 192;
 
 constexpr int kABytes = BM * BK * 2;
 constexpr int kBBytes = BNH * BK * 2;
 constexpr int kStageBytes = kABytes + kBBytes;
 constexpr int kBarrierOffset = kStages * kStageBytes;
-constexpr int kSmemTotal = kBarrierOffset + 256 + 1024;
+constexpr int kColsumOffset = kBarrierOffset + 256;
+constexpr int kSmemTotal = kColsumOffset + 4 * BN * 4 + 1024;
 
-struct Gemm2Params {
-  int M, N, K;
-  void* D;
-  long long ldd;
-  const float* bias;
-  const __nv_bfloat16* mask;
-  long long ldmask;
-  int relu;
-  int d_fp32;
-  int num_m_blocks, num_n_blocks;   // in 256-row / 256-column tiles
-  int group_m;
-};
-
-__device__ __forceinline__ void tile_coords2(const Gemm2Params& p, int t, int& m_blk, int& n_blk) {
-  const int per_group = p.group_m * p.num_n_blocks;
-  const int g = t / per_group;
-  const int r = t - g * per_group;
-  const int m_first = g * p.group_m;
-  const int gsize = min(p.group_m, p.num_m_blocks - m_first);
-  n_blk = r / gsize;
-  m_blk = m_first + (r - n_blk * gsize);
+// work unit -> tile (and which half of it, -1 = the whole tile)
+struct Unit { int m_blk, n_blk, half; };
+__device__ __forceinline__ Unit unit_of(const GemmParams& p, int u) {
+  Unit w;
+  int t = u;
+  w.half = -1;
+  if (u >= p.full_tiles) {
+    const int idx = u - p.full_tiles;
+    t = p.full_tiles + (idx >> 1);
+    w.half = idx & 1;
+  }
+  tile_coords(p, t, w.m_blk, w.n_blk);
+  return w;
 }
 
 __device__ __forceinline__ uint32_t cluster_ctarank() {
@@ -109,16 +108,10 @@ __device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {
       : "memory");
 }
 
-__device__ __forceinline__ uint64_t make_smem_desc2(uint32_t smem_addr, bool mn_major) {
-  const uint64_t lbo = mn_major ? uint64_t((BK * 128) >> 4) : 1ull;
-  const uint64_t sbo = 1024 >> 4;
-  return uint64_t((smem_addr & 0x3FFFF) >> 4) | (lbo << 16) | (sbo << 32) | (1ull << 46) | (2ull << 61);
-}
-
 template <bool A_MN, bool B_MN>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                      const Gemm2Params p) {
+                      const __grid_constant__ CUtensorMap tmBh, const GemmParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + kBarrierOffset);
@@ -126,6 +119,8 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   uint64_t* tmem_full = empty_bar + kStages;
   uint64_t* tmem_empty = tmem_full + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  int* cs_last = reinterpret_cast<int*>(tmem_slot + 1);
+  float* cs_smem = reinterpret_cast<float*>(smem + kColsumOffset);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -134,6 +129,7 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   const int cluster_id = blockIdx.x >> 1;
   const int num_clusters = gridDim.x >> 1;
   const int num_tiles = p.num_m_blocks * p.num_n_blocks;
+  const int num_units = p.full_tiles + 2 * (num_tiles - p.full_tiles);
   const int num_kb = (p.K + BK - 1) / BK;
   constexpr uint32_t kTmemCols = 2 * BN;
 
@@ -168,17 +164,19 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int t = cluster_id; t < num_tiles; t += num_clusters) {
-        int m_blk, n_blk;
-        tile_coords2(p, t, m_blk, n_blk);
-        const int m0 = m_blk * (2 * BM) + int(rank) * BM;      // this CTA's rows of A
-        const int n0 = n_blk * BN + int(rank) * BNH;           // this CTA's half of B
+      for (int u = cluster_id; u < num_units; u += num_clusters) {
+        const Unit w = unit_of(p, u);
+        const bool whole = w.half < 0;
+        const int b_rows = whole ? BNH : BNH / 2;              // B columns this CTA stages
+        const int m0 = w.m_blk * (2 * BM) + int(rank) * BM;    // this CTA's rows of A
+        const int n0 = w.n_blk * BN + (whole ? 0 : w.half * BNH) + int(rank) * b_rows;
+        const uint32_t tx = 2u * uint32_t(kABytes + b_rows * BK * 2);
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = smem + stage * kStageBytes;
           uint8_t* sb = sa + kABytes;
           const uint32_t leader_full = map_to_cta(smem_u32(&full_bar[stage]), 0);
-          if (leader) mbar_expect_tx(&full_bar[stage], 2 * kStageBytes);
+          if (leader) mbar_expect_tx(&full_bar[stage], tx);
           const int k0 = kb * BK;
           if constexpr (A_MN) {
 #pragma unroll
@@ -187,10 +185,10 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
             tma_load_2d_pair(sa, &tmA, leader_full, k0, m0);
           }
           if constexpr (B_MN) {
-#pragma unroll
-            for (int j = 0; j < BNH / 64; ++j) tma_load_2d_pair(sb + j * (BK * 128), &tmB, leader_full, n0 + j * 64, k0);
+            tma_load_2d_pair(sb, &tmB, leader_full, n0, k0);
+            if (whole) tma_load_2d_pair(sb + BK * 128, &tmB, leader_full, n0 + 64, k0);
           } else {
-            tma_load_2d_pair(sb, &tmB, leader_full, k0, n0);
+            tma_load_2d_pair(sb, whole ? &tmB : &tmBh, leader_full, k0, n0);
           }
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
@@ -199,15 +197,15 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   } else if (warp == 1) {
     // ===================== MMA issuer (leader CTA only) =====================
     if (leader && lane == 0) {
-      // c_format F32, a/b BF16, majors, N = 256 (>>3), M = 256 (>>4)
-      constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (uint32_t(A_MN) << 15) |
-                                 (uint32_t(B_MN) << 16) | (uint32_t(BN >> 3) << 17) | (uint32_t((2 * BM) >> 4) << 24);
+      constexpr uint32_t idesc_whole = make_idesc<T>(2 * BM, BN, A_MN, B_MN);
+      constexpr uint32_t idesc_half = make_idesc<T>(2 * BM, BN / 2, A_MN, B_MN);
       constexpr uint32_t a_step = A_MN ? (UMMA_K * 128) >> 4 : (UMMA_K * 2) >> 4;
       constexpr uint32_t b_step = B_MN ? (UMMA_K * 128) >> 4 : (UMMA_K * 2) >> 4;
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
-      for (int t = cluster_id; t < num_tiles; t += num_clusters, ++it) {
+      for (int u = cluster_id; u < num_units; u += num_clusters, ++it) {
+        const uint32_t idesc = u < p.full_tiles ? idesc_whole : idesc_half;
         const int as = it & 1;
         const uint32_t aphase = (it >> 1) & 1;
         mbar_wait(&tmem_empty[as], aphase ^ 1);
@@ -217,8 +215,8 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
           const uint32_t sa = smem_u32(smem + stage * kStageBytes);
-          const uint64_t adesc = make_smem_desc2(sa, A_MN);
-          const uint64_t bdesc = make_smem_desc2(sa + kABytes, B_MN);
+          const uint64_t adesc = make_smem_desc<BK>(sa, A_MN);
+          const uint64_t bdesc = make_smem_desc<BK>(sa + kABytes, B_MN);
 #pragma unroll
           for (int k = 0; k < BK / UMMA_K; ++k) {
             umma_bf16_pair(d_tmem, adesc + uint64_t(k * a_step), bdesc + uint64_t(k * b_step), idesc,
@@ -234,84 +232,27 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     // ===================== epilogue (warps 2..5, both CTAs) =====================
     const int quad = warp & 3;
     int it = 0;
-    for (int t = cluster_id; t < num_tiles; t += num_clusters, ++it) {
+    for (int u = cluster_id; u < num_units; u += num_clusters, ++it) {
       const int as = it & 1;
       const uint32_t aphase = (it >> 1) & 1;
-      int m_blk, n_blk;
-      tile_coords2(p, t, m_blk, n_blk);
-      const int m0 = m_blk * (2 * BM) + int(rank) * BM;
-      const int n0 = n_blk * BN;
-      const int row = m0 + quad * 32 + lane;
+      const Unit w = unit_of(p, u);
+      const int m0 = w.m_blk * (2 * BM) + int(rank) * BM;
+      const int strip = w.m_blk * 2 + int(rank);
       mbar_wait(&tmem_full[as], aphase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + (uint32_t(quad * 32) << 16) + uint32_t(as * BN);
-#pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
-        uint32_t v[32];
-        tmem_ld_32x32b_x32(taddr + c * 32, v);
-        tmem_ld_wait();
-        const int col0 = n0 + c * 32;
-        if (row < p.M && col0 < p.N) {
-          float f[32];
-#pragma unroll
-          for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
-          if (p.bias != nullptr) {
-#pragma unroll
-            for (int j = 0; j < 32; j += 4) {
-              if (col0 + j < p.N) {
-                const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + j));
-                f[j] += b4.x; f[j + 1] += b4.y; f[j + 2] += b4.z; f[j + 3] += b4.w;
-              }
-            }
-          }
-          if (p.relu) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.0f);
-          }
-          if (p.mask != nullptr) {
-            const __nv_bfloat16* mrow = p.mask + (long long)row * p.ldmask + col0;
-#pragma unroll
-            for (int j = 0; j < 32; j += 8) {
-              if (col0 + j < p.N) {
-                const uint4 m4 = __ldg(reinterpret_cast<const uint4*>(mrow + j));
-                const uint32_t mw[4] = {m4.x, m4.y, m4.z, m4.w};
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                  if (!(bf16_lo(mw[q]) > 0.0f)) f[j + 2 * q] = 0.0f;
-                  if (!(bf16_hi(mw[q]) > 0.0f)) f[j + 2 * q + 1] = 0.0f;
-                }
-              }
-            }
-          }
-          if (p.d_fp32) {
-            float* drow = reinterpret_cast<float*>(p.D) + (long long)row * p.ldd + col0;
-#pragma unroll
-            for (int j = 0; j < 32; j += 4) {
-              if (col0 + j < p.N)
-                *reinterpret_cast<float4*>(drow + j) = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
-            }
-          } else {
-            __nv_bfloat16* drow = reinterpret_cast<__nv_bfloat16*>(p.D) + (long long)row * p.ldd + col0;
-#pragma unroll
-            for (int j = 0; j < 32; j += 8) {
-              if (col0 + j < p.N) {
-                uint4 o;
-                o.x = pack_bf16x2(f[j], f[j + 1]);
-                o.y = pack_bf16x2(f[j + 2], f[j + 3]);
-                o.z = pack_bf16x2(f[j + 4], f[j + 5]);
-                o.w = pack_bf16x2(f[j + 6], f[j + 7]);
-                *reinterpret_cast<uint4*>(drow + j) = o;
-              }
-            }
-          }
+      uint64_t* release_bar = &tmem_empty[as];
+      auto release = [&]() {
+        if (lane == 0) {
+          if (leader) mbar_arrive(release_bar);
+          else mbar_arrive_cluster(map_to_cta(smem_u32(release_bar), 0));
         }
-      }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) {
-        if (leader) mbar_arrive(&tmem_empty[as]);
-        else mbar_arrive_cluster(map_to_cta(smem_u32(&tmem_empty[as]), 0));
-      }
+      };
+      if (w.half < 0)
+        epilogue_tile<T, BN>(p, taddr, m0, w.n_blk * BN, w.n_blk, strip, quad, lane, cs_smem, cs_last, release);
+      else      // half tiles are never combined with the fused column sums (see launch_pair)
+        epilogue_tile<T, BN / 2>(p, taddr, m0, w.n_blk * BN + w.half * BNH, 0, strip, quad, lane, cs_smem, cs_last,
+                                 release);
     }
   }
 
@@ -324,65 +265,42 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   }
 }
 
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-int make_tensor_map2(CUtensorMap* out, const void* base, long long rows, long long cols, long long ld, int box_rows) {
-  static EncodeTiledFn enc = nullptr;
-  if (!enc) {
-    void* sym = nullptr;
-    cudaDriverEntryPointQueryResult q;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &q) != cudaSuccess ||
-        q != cudaDriverEntryPointSuccess)
-      return fail("cuTensorMapEncodeTiled is not available from the driver");
-    enc = reinterpret_cast<EncodeTiledFn>(sym);
-  }
-  cuuint64_t dims[2] = {cuuint64_t(cols), cuuint64_t(rows)};
-  cuuint64_t strides[1] = {cuuint64_t(ld) * 2};
-  cuuint32_t box[2] = {64u, cuuint32_t(box_rows)};
-  cuuint32_t estr[2] = {1u, 1u};
-  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) return fail("cuTensorMapEncodeTiled failed with CUresult %d", int(r));
-  return B200DP_OK;
-}
-
 template <bool A_MN, bool B_MN>
 int launch_pair(const b200dp_gemm_args* a, cudaStream_t stream) {
-  CUtensorMap tmA, tmB;
+  CUtensorMap tmA, tmB, tmBh;
   int rc;
-  if (A_MN) rc = make_tensor_map2(&tmA, a->A, a->K, a->M, a->lda, BK);
-  else rc = make_tensor_map2(&tmA, a->A, a->M, a->K, a->lda, BM);
+  if (A_MN) rc = get_tensor_map(&tmA, Elem<T>::kTma, 2, a->A, a->K, a->M, a->lda, BK);
+  else rc = get_tensor_map(&tmA, Elem<T>::kTma, 2, a->A, a->M, a->K, a->lda, BM);
   if (rc) return rc;
-  if (B_MN) rc = make_tensor_map2(&tmB, a->B, a->K, a->N, a->ldb, BK);
-  else rc = make_tensor_map2(&tmB, a->B, a->N, a->K, a->ldb, BNH);
+  if (B_MN) rc = get_tensor_map(&tmB, Elem<T>::kTma, 2, a->B, a->K, a->N, a->ldb, BK);
+  else rc = get_tensor_map(&tmB, Elem<T>::kTma, 2, a->B, a->N, a->K, a->ldb, BNH);
   if (rc) return rc;
-  Gemm2Params p;
-  p.M = a->M; p.N = a->N; p.K = a->K;
-  p.D = a->D; p.ldd = a->ldd;
-  p.bias = a->bias;
-  p.mask = reinterpret_cast<const __nv_bfloat16*>(a->mask_src);
-  p.ldmask = a->ldmask;
-  p.relu = a->relu; p.d_fp32 = a->d_fp32;
+  GemmParams p;
+  fill_gemm_params(a, &p);
   p.num_m_blocks = (a->M + 2 * BM - 1) / (2 * BM);
   p.num_n_blocks = (a->N + BN - 1) / BN;
   p.group_m = 8;
+  p.cs_ld = p.num_n_blocks * BN;
   const int tiles = p.num_m_blocks * p.num_n_blocks;
   int clusters = (a->max_ctas > 0 ? a->max_ctas : sm_count()) / 2;
   if (clusters < 1) clusters = 1;
-  if (clusters > tiles) clusters = tiles;
-  auto kern = gemm_bf16_pair_kernel<A_MN, B_MN>;
-  static bool attr_set_dev[64] = {false};     // per device: the attribute belongs to the device's context
-  int dev_ = 0;
-  cudaGetDevice(&dev_);
-  bool& attr_set = attr_set_dev[dev_ & 63];
-  if (!attr_set) {
-    B200DP_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
-    attr_set = true;
+  // tail wave as half tiles when that halves its cost (never with the fused column sums, whose
+  // tickets count whole 256-column blocks)
+  p.full_tiles = tiles;
+  const int rem = tiles % clusters;
+  if (a->split_tail >= 0 && tiles > clusters && rem > 0 && 2 * rem <= clusters && a->colsum_out == nullptr)
+    p.full_tiles = tiles - rem;
+  tmBh = tmB;
+  if (!B_MN && p.full_tiles < tiles) {
+    rc = get_tensor_map(&tmBh, Elem<T>::kTma, 2, a->B, a->N, a->K, a->ldb, BNH / 2);
+    if (rc) return rc;
   }
-  kern<<<2 * clusters, kThreads, kSmemTotal, stream>>>(tmA, tmB, p);
+  const int units = p.full_tiles + 2 * (tiles - p.full_tiles);
+  if (clusters > units) clusters = units;
+  auto kern = gemm_bf16_pair_kernel<A_MN, B_MN>;
+  static bool attr_done[64] = {false};
+  if (int e = ensure_smem_attr(kern, kSmemTotal, attr_done)) return e;
+  kern<<<2 * clusters, kGemmThreads, kSmemTotal, stream>>>(tmA, tmB, tmBh, p);
   B200DP_CUDA_OK(cudaGetLastError());
   return B200DP_OK;
 }

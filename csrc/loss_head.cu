@@ -7,7 +7,8 @@
 //                        e.g. 4096 -> 1): a GEMV per row on CUDA cores (tensor cores cannot be fed by
 //                        N = 1), fused with bias, the MSE loss and dY (ref.py:44,170,173,176).
 //  * head_bwd          - backward of that layer in ONE pass over its input H: dH = (dY W) * [H>0]
-//                        (bf16) and per-row-strip partial sums of dW = dY^T H and db = sum dY.
+//                        (bf16) and per-row-strip partial sums of dW = dY^T H, db = sum dY and - for the
+//                        bias gradient of the layer below - the column sums of dH.
 //  * colsum / reduce_partials - bias gradient of the GEMM layers (db = column sums of dY) and the
 //                        fixed-order reduction of any [strips][n] partial buffer.
 #include "common.cuh"
@@ -16,6 +17,28 @@ namespace b200dp {
 namespace {
 
 constexpr int kRedThreads = 256;
+
+// 8 consecutive elements of a bf16 (bf16 training) or fp32 (fp32 / TF32 training) row as floats
+template <typename T> __device__ __forceinline__ void load8(const T* p, float (&o)[8]);
+template <> __device__ __forceinline__ void load8<__nv_bfloat16>(const __nv_bfloat16* p, float (&o)[8]) {
+  const uint4 v = __ldg(reinterpret_cast<const uint4*>(p));
+  o[0] = bf16_lo(v.x); o[1] = bf16_hi(v.x); o[2] = bf16_lo(v.y); o[3] = bf16_hi(v.y);
+  o[4] = bf16_lo(v.z); o[5] = bf16_hi(v.z); o[6] = bf16_lo(v.w); o[7] = bf16_hi(v.w);
+}
+template <> __device__ __forceinline__ void load8<float>(const float* p, float (&o)[8]) {
+  const float4 a = __ldg(reinterpret_cast<const float4*>(p));
+  const float4 b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+  o[0] = a.x; o[1] = a.y; o[2] = a.z; o[3] = a.w; o[4] = b.x; o[5] = b.y; o[6] = b.z; o[7] = b.w;
+}
+template <typename T> __device__ __forceinline__ void store8(T* p, const float (&v)[8]);
+template <> __device__ __forceinline__ void store8<__nv_bfloat16>(__nv_bfloat16* p, const float (&v)[8]) {
+  *reinterpret_cast<uint4*>(p) = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]),
+                                            pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+}
+template <> __device__ __forceinline__ void store8<float>(float* p, const float (&v)[8]) {
+  reinterpret_cast<float4*>(p)[0] = make_float4(v[0], v[1], v[2], v[3]);
+  reinterpret_cast<float4*>(p)[1] = make_float4(v[4], v[5], v[6], v[7]);
+}
 
 // block-wide sum; result valid in thread 0
 __device__ __forceinline__ float block_sum(float v, float* red) {
@@ -51,7 +74,7 @@ __device__ __forceinline__ void finish_scalar(float block_val, float scale, floa
 template <bool PRED_BF16, bool DY_BF16>
 __global__ void __launch_bounds__(kRedThreads)
 mse_kernel(const void* __restrict__ pred, const float* __restrict__ target, long long n, float inv_n,
-           void* __restrict__ dy, float* __restrict__ loss, float* partials, unsigned int* ticket) {
+           float gscale, void* __restrict__ dy, float* __restrict__ loss, float* partials, unsigned int* ticket) {
   __shared__ float red[kRedThreads / 32];
   __shared__ bool is_last;
   float acc = 0.0f;
@@ -61,7 +84,7 @@ mse_kernel(const void* __restrict__ pred, const float* __restrict__ target, long
                               : reinterpret_cast<const float*>(pred)[i];
     const float d = p - target[i];
     acc = fmaf(d, d, acc);
-    const float g = 2.0f * d * inv_n;
+    const float g = 2.0f * d * gscale;
     if (DY_BF16) reinterpret_cast<__nv_bfloat16*>(dy)[i] = __float2bfloat16_rn(g);
     else reinterpret_cast<float*>(dy)[i] = g;
   }
@@ -70,12 +93,12 @@ mse_kernel(const void* __restrict__ pred, const float* __restrict__ target, long
 }
 
 // ---- head forward: one warp per row ----
-template <int NOUT>
+template <typename T, int NOUT>
 __global__ void __launch_bounds__(kRedThreads)
-head_fwd_kernel(const __nv_bfloat16* __restrict__ H, long long ldh, const __nv_bfloat16* __restrict__ W,
+head_fwd_kernel(const T* __restrict__ H, long long ldh, const T* __restrict__ W,
                 const float* __restrict__ bias, const float* __restrict__ target, int rows, int K,
-                float inv_n, float* __restrict__ yhat, float* __restrict__ dy, float* __restrict__ loss,
-                float* partials, unsigned int* ticket) {
+                float inv_n, float gscale, float* __restrict__ yhat, float* __restrict__ dy,
+                float* __restrict__ loss, float* partials, unsigned int* ticket) {
   __shared__ float red[kRedThreads / 32];
   __shared__ bool is_last;
   const int lane = threadIdx.x & 31;
@@ -84,23 +107,20 @@ head_fwd_kernel(const __nv_bfloat16* __restrict__ H, long long ldh, const __nv_b
   const int nw = gridDim.x * warps_per_block;
   float acc_loss = 0.0f;
   for (int r = gw; r < rows; r += nw) {
-    const __nv_bfloat16* h = H + (long long)r * ldh;
+    const T* h = H + (long long)r * ldh;
     float s[NOUT];
 #pragma unroll
     for (int o = 0; o < NOUT; ++o) s[o] = 0.0f;
 #pragma unroll 4
     for (int k = lane * 8; k < K; k += 256) {
-      const uint4 hv = __ldg(reinterpret_cast<const uint4*>(h + k));
-      const uint32_t hw[4] = {hv.x, hv.y, hv.z, hv.w};
+      float hv[8];
+      load8<T>(h + k, hv);
 #pragma unroll
       for (int o = 0; o < NOUT; ++o) {
-        const uint4 wv = __ldg(reinterpret_cast<const uint4*>(W + (long long)o * K + k));
-        const uint32_t ww[4] = {wv.x, wv.y, wv.z, wv.w};
+        float wv[8];
+        load8<T>(W + (long long)o * K + k, wv);
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          s[o] = fmaf(bf16_lo(hw[q]), bf16_lo(ww[q]), s[o]);
-          s[o] = fmaf(bf16_hi(hw[q]), bf16_hi(ww[q]), s[o]);
-        }
+        for (int q = 0; q < 8; ++q) s[o] = fmaf(hv[q], wv[q], s[o]);
       }
     }
 #pragma unroll
@@ -111,7 +131,7 @@ head_fwd_kernel(const __nv_bfloat16* __restrict__ H, long long ldh, const __nv_b
         const float p = s[o] + bias[o];
         const float d = p - target[(long long)r * NOUT + o];
         yhat[(long long)r * NOUT + o] = p;
-        dy[(long long)r * NOUT + o] = 2.0f * d * inv_n;
+        dy[(long long)r * NOUT + o] = 2.0f * d * gscale;
         acc_loss = fmaf(d, d, acc_loss);
       }
     }
@@ -124,12 +144,13 @@ head_fwd_kernel(const __nv_bfloat16* __restrict__ H, long long ldh, const __nv_b
 constexpr int kHeadBwdThreads = 256;
 constexpr int kHeadBwdCols = kHeadBwdThreads * 8;
 
-template <int NOUT>
+template <typename T, int NOUT>
 __global__ void __launch_bounds__(kHeadBwdThreads)
-head_bwd_kernel(const float* __restrict__ dy, const __nv_bfloat16* __restrict__ W,
-                const __nv_bfloat16* __restrict__ H, long long ldh, int rows, int K, int rows_per_strip,
-                __nv_bfloat16* __restrict__ dH, long long lddh, float* __restrict__ partials) {
-  // partials layout: [strip][NOUT][K + 1]; column K holds the bias-gradient partial
+head_bwd_kernel(const float* __restrict__ dy, const T* __restrict__ W,
+                const T* __restrict__ H, long long ldh, int rows, int K, int rows_per_strip,
+                T* __restrict__ dH, long long lddh, float* __restrict__ partials, int prow) {
+  // partials layout: [strip][prow][K + 1], prow = NOUT (+1: column sums of dH); column K of the first
+  // NOUT rows holds the bias-gradient partial
   const int strip = blockIdx.x;
   const int k0 = blockIdx.y * kHeadBwdCols + threadIdx.x * 8;
   const int r_begin = strip * rows_per_strip;
@@ -139,19 +160,16 @@ head_bwd_kernel(const float* __restrict__ dy, const __nv_bfloat16* __restrict__ 
   float acc[NOUT][8];
 #pragma unroll
   for (int o = 0; o < NOUT; ++o) {
-    uint4 wv = make_uint4(0, 0, 0, 0);
-    if (active) wv = __ldg(reinterpret_cast<const uint4*>(W + (long long)o * K + k0));
-    const uint32_t ww[4] = {wv.x, wv.y, wv.z, wv.w};
 #pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      w[o][2 * q] = bf16_lo(ww[q]);
-      w[o][2 * q + 1] = bf16_hi(ww[q]);
-      acc[o][2 * q] = acc[o][2 * q + 1] = 0.0f;
-    }
+    for (int q = 0; q < 8; ++q) w[o][q] = acc[o][q] = 0.0f;
+    if (active) load8<T>(W + (long long)o * K + k0, w[o]);
   }
   float bacc[NOUT];
 #pragma unroll
   for (int o = 0; o < NOUT; ++o) bacc[o] = 0.0f;
+  float dhsum[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) dhsum[j] = 0.0f;
 
 #pragma unroll 4
   for (int r = r_begin; r < r_end; ++r) {
@@ -163,11 +181,8 @@ head_bwd_kernel(const float* __restrict__ dy, const __nv_bfloat16* __restrict__ 
       for (int o = 0; o < NOUT; ++o) bacc[o] += g[o];
     }
     if (!active) continue;
-    const uint4 hv = __ldg(reinterpret_cast<const uint4*>(H + (long long)r * ldh + k0));
-    const uint32_t hw[4] = {hv.x, hv.y, hv.z, hv.w};
     float h[8];
-#pragma unroll
-    for (int q = 0; q < 4; ++q) { h[2 * q] = bf16_lo(hw[q]); h[2 * q + 1] = bf16_hi(hw[q]); }
+    load8<T>(H + (long long)r * ldh + k0, h);
     float dh[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) dh[j] = 0.0f;
@@ -181,14 +196,14 @@ head_bwd_kernel(const float* __restrict__ dy, const __nv_bfloat16* __restrict__ 
     }
     if (dH != nullptr) {
 #pragma unroll
-      for (int j = 0; j < 8; ++j) dh[j] = h[j] > 0.0f ? dh[j] : 0.0f;
-      uint4 o4;
-      o4.x = pack_bf16x2(dh[0], dh[1]); o4.y = pack_bf16x2(dh[2], dh[3]);
-      o4.z = pack_bf16x2(dh[4], dh[5]); o4.w = pack_bf16x2(dh[6], dh[7]);
-      *reinterpret_cast<uint4*>(dH + (long long)r * lddh + k0) = o4;
+      for (int j = 0; j < 8; ++j) {
+        dh[j] = h[j] > 0.0f ? dh[j] : 0.0f;
+        dhsum[j] += dh[j];
+      }
+      store8<T>(dH + (long long)r * lddh + k0, dh);
     }
   }
-  float* my = partials + (long long)strip * NOUT * (K + 1);
+  float* my = partials + (long long)strip * prow * (K + 1);
   if (active) {
 #pragma unroll
     for (int o = 0; o < NOUT; ++o) {
@@ -196,6 +211,11 @@ head_bwd_kernel(const float* __restrict__ dy, const __nv_bfloat16* __restrict__ 
       float* d = my + (long long)o * (K + 1) + k0;
 #pragma unroll
       for (int j = 0; j < 8; ++j) d[j] = acc[o][j];
+    }
+    if (prow > NOUT) {
+      float* d = my + (long long)NOUT * (K + 1) + k0;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) d[j] = dhsum[j];
     }
   }
   if (blockIdx.y == 0 && threadIdx.x == 0) {
@@ -239,25 +259,29 @@ reduce_partials_kernel(const float* __restrict__ partials, int strips, long long
   else reinterpret_cast<float*>(out)[j] = s;
 }
 
-// same reduction; scatters the "[NOUT][K+1]" head partials into the weight / bias gradient slots
+// same reduction; scatters the "[prow][K+1]" head partials into the weight / bias gradient slots (row
+// `nout`, when present, holds the column sums of dH = the bias gradient of the layer below)
 template <bool OUT_BF16>
 __global__ void __launch_bounds__(kRedCols * kRedGroups)
-head_reduce_kernel(const float* __restrict__ partials, int strips, int nout, int K, void* dW, void* db) {
+head_reduce_kernel(const float* __restrict__ partials, int strips, int nout, int prow, int K, void* dW, void* db,
+                   void* db_prev) {
   __shared__ float sm[kRedGroups][kRedCols];
-  const long long n = (long long)nout * (K + 1);
+  const long long n = (long long)prow * (K + 1);
   const long long j = (long long)blockIdx.x * kRedCols + threadIdx.x % kRedCols;
   const float s = strided_strip_sum(partials, strips, n, j, sm);
   if (threadIdx.x >= kRedCols || j >= n) return;
   const int o = int(j / (K + 1)), k = int(j % (K + 1));
-  void* dst = k < K ? dW : db;
-  const long long idx = k < K ? (long long)o * K + k : o;
+  if (o >= nout && k >= K) return;
+  void* dst = o >= nout ? db_prev : (k < K ? dW : db);
+  const long long idx = o >= nout ? k : (k < K ? (long long)o * K + k : o);
   if (OUT_BF16) reinterpret_cast<__nv_bfloat16*>(dst)[idx] = __float2bfloat16_rn(s);
   else reinterpret_cast<float*>(dst)[idx] = s;
 }
 
-// column sums of a bf16 [rows, n] matrix over a strip of rows -> partials[strip][n]
+// column sums of a bf16 / fp32 [rows, n] matrix over a strip of rows -> partials[strip][n]
+template <typename T>
 __global__ void __launch_bounds__(256)
-colsum_kernel(const __nv_bfloat16* __restrict__ A, long long lda, int rows, int n, int rows_per_strip,
+colsum_kernel(const T* __restrict__ A, long long lda, int rows, int n, int rows_per_strip,
               float* __restrict__ partials) {
   const int c0 = (blockIdx.y * blockDim.x + threadIdx.x) * 8;
   if (c0 >= n) return;
@@ -267,10 +291,10 @@ colsum_kernel(const __nv_bfloat16* __restrict__ A, long long lda, int rows, int 
 #pragma unroll
   for (int j = 0; j < 8; ++j) acc[j] = 0.0f;
   for (int r = r_begin; r < r_end; ++r) {
-    const uint4 v = __ldg(reinterpret_cast<const uint4*>(A + (long long)r * lda + c0));
-    const uint32_t u[4] = {v.x, v.y, v.z, v.w};
+    float v[8];
+    load8<T>(A + (long long)r * lda + c0, v);
 #pragma unroll
-    for (int q = 0; q < 4; ++q) { acc[2 * q] += bf16_lo(u[q]); acc[2 * q + 1] += bf16_hi(u[q]); }
+    for (int q = 0; q < 8; ++q) acc[q] += v[q];
   }
   float* dst = partials + (long long)blockIdx.x * n + c0;
   *reinterpret_cast<float4*>(dst) = make_float4(acc[0], acc[1], acc[2], acc[3]);
@@ -291,8 +315,8 @@ using namespace b200dp;
 extern "C" long long b200dp_mse_scratch_bytes(long long numel) { return 256 + 4ll * reduce_grid(numel); }
 
 extern "C" int b200dp_mse_loss_grad(const void* pred, int pred_bf16, const float* target, long long numel,
-                                    void* dy, int dy_bf16, float* loss, void* scratch, long long scratch_bytes,
-                                    void* stream) {
+                                    long long denom, void* dy, int dy_bf16, float* loss, float grad_scale,
+                                    void* scratch, long long scratch_bytes, void* stream) {
   B200DP_REQUIRE(pred && target && dy && loss && scratch, "mse: null pointer");
   B200DP_REQUIRE(numel >= 1, "mse: numel must be >= 1");
   const int grid = reduce_grid(numel);
@@ -300,9 +324,10 @@ extern "C" int b200dp_mse_loss_grad(const void* pred, int pred_bf16, const float
                  256 + 4ll * grid);
   unsigned int* ticket = reinterpret_cast<unsigned int*>(scratch);
   float* partials = reinterpret_cast<float*>(reinterpret_cast<char*>(scratch) + 256);
-  const float inv_n = 1.0f / float(numel);
+  const float inv_n = 1.0f / float(denom > 0 ? denom : numel);
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-#define LAUNCH(PB, DB) mse_kernel<PB, DB><<<grid, kRedThreads, 0, s>>>(pred, target, numel, inv_n, dy, loss, partials, ticket)
+  const float gscale = inv_n * grad_scale;
+#define LAUNCH(PB, DB) mse_kernel<PB, DB><<<grid, kRedThreads, 0, s>>>(pred, target, numel, inv_n, gscale, dy, loss, partials, ticket)
   if (pred_bf16 && dy_bf16) LAUNCH(true, true);
   else if (pred_bf16) LAUNCH(true, false);
   else if (dy_bf16) LAUNCH(false, true);
@@ -315,12 +340,13 @@ extern "C" int b200dp_mse_loss_grad(const void* pred, int pred_bf16, const float
 extern "C" long long b200dp_head_scratch_bytes(int rows, int K, int nout) {
   const int strips = (rows + 31) / 32;
   const long long fwd = 256 + 4ll * 4 * sm_count();
-  return fwd + 4ll * strips * nout * (K + 1);
+  return fwd + 4ll * strips * (nout + 1) * (K + 1);
 }
 
-extern "C" int b200dp_head_fwd_mse(const void* H, long long ldh, const void* W, const float* bias,
+extern "C" int b200dp_head_fwd_mse(const void* H, long long ldh, const void* W, int elems_fp32, const float* bias,
                                    const float* target, int rows, int K, int nout, float* yhat, float* dy,
-                                   float* loss, void* scratch, long long scratch_bytes, void* stream) {
+                                   float* loss, float grad_scale, void* scratch, long long scratch_bytes,
+                                   void* stream) {
   B200DP_REQUIRE(H && W && bias && target && yhat && dy && loss && scratch, "head_fwd: null pointer");
   B200DP_REQUIRE(nout >= 1 && nout <= 4, "head_fwd: supports 1..4 outputs (got %d)", nout);
   B200DP_REQUIRE(K % 8 == 0 && ldh % 8 == 0, "head_fwd: K and ldh must be multiples of 8");
@@ -332,50 +358,54 @@ extern "C" int b200dp_head_fwd_mse(const void* H, long long ldh, const void* W, 
   float* partials = reinterpret_cast<float*>(reinterpret_cast<char*>(scratch) + 256);
   const float inv_n = 1.0f / (float(rows) * float(nout));
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-  const __nv_bfloat16* h = reinterpret_cast<const __nv_bfloat16*>(H);
-  const __nv_bfloat16* w = reinterpret_cast<const __nv_bfloat16*>(W);
-#define LAUNCH(NO) head_fwd_kernel<NO><<<grid, kRedThreads, 0, s>>>(h, ldh, w, bias, target, rows, K, inv_n, yhat, dy, loss, partials, ticket)
+  const float gscale = inv_n * grad_scale;
+#define LAUNCH(TT, NO) head_fwd_kernel<TT, NO><<<grid, kRedThreads, 0, s>>>(reinterpret_cast<const TT*>(H), ldh, reinterpret_cast<const TT*>(W), bias, target, rows, K, inv_n, gscale, yhat, dy, loss, partials, ticket)
+#define LAUNCH_T(NO) do { if (elems_fp32) LAUNCH(float, NO); else LAUNCH(__nv_bfloat16, NO); } while (0)
   switch (nout) {
-    case 1: LAUNCH(1); break;
-    case 2: LAUNCH(2); break;
-    case 3: LAUNCH(3); break;
-    default: LAUNCH(4); break;
+    case 1: LAUNCH_T(1); break;
+    case 2: LAUNCH_T(2); break;
+    case 3: LAUNCH_T(3); break;
+    default: LAUNCH_T(4); break;
   }
+#undef LAUNCH_T
 #undef LAUNCH
   B200DP_CUDA_OK(cudaGetLastError());
   return B200DP_OK;
 }
 
-extern "C" int b200dp_head_bwd(const float* dy, const void* W, const void* H, long long ldh, int rows, int K,
-                               int nout, void* dH, long long lddh, void* dW, void* db, int grads_bf16,
-                               void* scratch, long long scratch_bytes, void* stream) {
+extern "C" int b200dp_head_bwd(const float* dy, const void* W, const void* H, long long ldh, int elems_fp32,
+                               int rows, int K, int nout, void* dH, long long lddh, void* dW, void* db, void* db_prev,
+                               int grads_bf16, void* scratch, long long scratch_bytes, void* stream) {
   B200DP_REQUIRE(dy && W && H && dW && db && scratch, "head_bwd: null pointer");
+  B200DP_REQUIRE(db_prev == nullptr || dH != nullptr, "head_bwd: db_prev (column sums of dH) needs dH");
   B200DP_REQUIRE(nout >= 1 && nout <= 4, "head_bwd: supports 1..4 outputs (got %d)", nout);
   B200DP_REQUIRE(K % 8 == 0 && ldh % 8 == 0 && (dH == nullptr || lddh % 8 == 0),
                  "head_bwd: K, ldh, lddh must be multiples of 8");
   const int rows_per_strip = 32;
   const int strips = (rows + rows_per_strip - 1) / rows_per_strip;
   const long long fwd = 256 + 4ll * 4 * sm_count();
-  B200DP_REQUIRE(scratch_bytes >= fwd + 4ll * strips * nout * (K + 1), "head_bwd: scratch too small");
+  const int prow = nout + (db_prev != nullptr ? 1 : 0);
+  B200DP_REQUIRE(scratch_bytes >= fwd + 4ll * strips * prow * (K + 1), "head_bwd: scratch too small");
   float* partials = reinterpret_cast<float*>(reinterpret_cast<char*>(scratch) + fwd);
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   dim3 grid(strips, (K + kHeadBwdCols - 1) / kHeadBwdCols);
-  const __nv_bfloat16* w = reinterpret_cast<const __nv_bfloat16*>(W);
-  const __nv_bfloat16* h = reinterpret_cast<const __nv_bfloat16*>(H);
-  __nv_bfloat16* dh = reinterpret_cast<__nv_bfloat16*>(dH);
-#define LAUNCH(NO) head_bwd_kernel<NO><<<grid, kHeadBwdThreads, 0, s>>>(dy, w, h, ldh, rows, K, rows_per_strip, dh, lddh, partials)
+#define LAUNCH(TT, NO) head_bwd_kernel<TT, NO><<<grid, kHeadBwdThreads, 0, s>>>(dy, reinterpret_cast<const TT*>(W), reinterpret_cast<const TT*>(H), ldh, rows, K, rows_per_strip, reinterpret_cast<TT*>(dH), lddh, partials, prow)
+#define LAUNCH_T(NO) do { if (elems_fp32) LAUNCH(float, NO); else LAUNCH(__nv_bfloat16, NO); } while (0)
   switch (nout) {
-    case 1: LAUNCH(1); break;
-    case 2: LAUNCH(2); break;
-    case 3: LAUNCH(3); break;
-    default: LAUNCH(4); break;
+    case 1: LAUNCH_T(1); break;
+    case 2: LAUNCH_T(2); break;
+    case 3: LAUNCH_T(3); break;
+    default: LAUNCH_T(4); break;
   }
+#undef LAUNCH_T
 #undef LAUNCH
   B200DP_CUDA_OK(cudaGetLastError());
-  const long long n = (long long)nout * (K + 1);
+  const long long n = (long long)prow * (K + 1);
   const int rgrid = int((n + kRedCols - 1) / kRedCols);
-  if (grads_bf16) head_reduce_kernel<true><<<rgrid, kRedCols * kRedGroups, 0, s>>>(partials, strips, nout, K, dW, db);
-  else head_reduce_kernel<false><<<rgrid, kRedCols * kRedGroups, 0, s>>>(partials, strips, nout, K, dW, db);
+  if (grads_bf16)
+    head_reduce_kernel<true><<<rgrid, kRedCols * kRedGroups, 0, s>>>(partials, strips, nout, prow, K, dW, db, db_prev);
+  else
+    head_reduce_kernel<false><<<rgrid, kRedCols * kRedGroups, 0, s>>>(partials, strips, nout, prow, K, dW, db, db_prev);
   B200DP_CUDA_OK(cudaGetLastError());
   return B200DP_OK;
 }
@@ -385,8 +415,8 @@ extern "C" long long b200dp_colsum_scratch_bytes(int rows, int n) {
   return 4ll * strips * n;
 }
 
-extern "C" int b200dp_colsum_bf16(const void* A, long long lda, int rows, int n, void* out, int out_bf16,
-                                  void* scratch, long long scratch_bytes, void* stream) {
+extern "C" int b200dp_colsum(const void* A, int a_fp32, long long lda, int rows, int n, void* out, int out_bf16,
+                             void* scratch, long long scratch_bytes, void* stream) {
   B200DP_REQUIRE(A && out && scratch, "colsum: null pointer");
   B200DP_REQUIRE(n % 8 == 0 && lda % 8 == 0, "colsum: n and lda must be multiples of 8");
   const int rows_per_strip = 64;
@@ -395,8 +425,8 @@ extern "C" int b200dp_colsum_bf16(const void* A, long long lda, int rows, int n,
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   float* partials = reinterpret_cast<float*>(scratch);
   dim3 grid(strips, (n / 8 + 255) / 256);
-  colsum_kernel<<<grid, 256, 0, s>>>(reinterpret_cast<const __nv_bfloat16*>(A), lda, rows, n, rows_per_strip,
-                                     partials);
+  if (a_fp32) colsum_kernel<float><<<grid, 256, 0, s>>>(reinterpret_cast<const float*>(A), lda, rows, n, rows_per_strip, partials);
+  else colsum_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>(reinterpret_cast<const __nv_bfloat16*>(A), lda, rows, n, rows_per_strip, partials);
   B200DP_CUDA_OK(cudaGetLastError());
   const int rgrid = (n + kRedCols - 1) / kRedCols;
   if (out_bf16) reduce_partials_kernel<true><<<rgrid, kRedCols * kRedGroups, 0, s>>>(partials, strips, n, out);

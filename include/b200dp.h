@@ -55,9 +55,25 @@ typedef struct b200dp_gemm_args {
   int tile_n;           /* 0 = auto, 128 or 256 */
   int max_ctas;         /* 0 = one persistent CTA per SM; >0 caps the grid (SM budget when overlapping) */
   int cta_group;        /* 0 = auto; 1 = one CTA per 128x256 tile; 2 = CTA pair (cta_group::2) per 256x256 tile */
+  int split_tail;       /* CTA-pair kernel: 0 = auto (a last wave that would keep <= half of the SM pairs busy runs
+                           as half-width tiles), -1 = never */
+  /* Fused bias gradient (the `sum` of AddmmBackward0, ref.py:176): when colsum_out is set the
+   * epilogue also writes colsum_out[n] = sum_m D[m,n] (the values it stores, before rounding), i.e.
+   * the db of the layer whose dY this GEMM produces.  Fixed summation order (bit-reproducible).
+   * colsum_scratch: b200dp_gemm_colsum_scratch_bytes(M, N) bytes whose first 4096 bytes are zero
+   * before the first use (ticket counters; every launch leaves them zero). */
+  void* colsum_out;     /* bf16 or fp32 [N], or NULL */
+  int colsum_out_bf16;
+  void* colsum_scratch;
+  long long colsum_scratch_bytes;
 } b200dp_gemm_args;
 
 int b200dp_gemm_bf16(const b200dp_gemm_args* args, void* stream);
+long long b200dp_gemm_colsum_scratch_bytes(int M, int N);
+/* Same contract with fp32 A, B and mask_src and an fp32 D: the tensor cores read the operands as TF32
+ * (kind::tf32) and accumulate in fp32.  The reference computes in fp32 only (ref.py:159); this is the
+ * path of fp32 models beyond the fused SIMT kernel.  lda/ldb/ldmask multiples of 4 elements. */
+int b200dp_gemm_tf32(const b200dp_gemm_args* args, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Whole-network SIMT kernel for MLPs too small for tensor cores (the reference's own 2-3-1 net,
@@ -95,32 +111,41 @@ int b200dp_tiny_mlp_fwd_bwd_noalloc(const b200dp_mlp_desc* m, const float* param
 
 /* ------------------------------------------------------------------------------------------------
  * Fused MSE loss + gradient (nn.MSELoss() + MseLossBackward, ref.py:94,173,176):
- *   *loss = mean((pred-target)^2),  dy = 2 (pred-target) / numel.
+ *   *loss = mean((pred-target)^2),  dy = grad_scale * 2 (pred-target) / numel.
+ * denom > 0 replaces numel as the divisor (outputs padded with zero predictions against zero targets
+ * add nothing to the sum but must not enter the mean).
+ * grad_scale is 1 for plain training; a rank whose gradient enters the all-reduce with weight w_r
+ * (sample weighting of uneven shards) passes w_r here, so the gradients arrive pre-weighted and any
+ * reduction - including the NVSwitch's unweighted sum - yields the weighted mean.
  * Deterministic two-stage reduction through `scratch` (b200dp_mse_scratch_bytes(numel) bytes; the
  * first 4 bytes are a ticket counter that must start at zero and is left at zero).
  */
 long long b200dp_mse_scratch_bytes(long long numel);
-int b200dp_mse_loss_grad(const void* pred, int pred_bf16, const float* target, long long numel, void* dy,
-                         int dy_bf16, float* loss, void* scratch, long long scratch_bytes, void* stream);
+int b200dp_mse_loss_grad(const void* pred, int pred_bf16, const float* target, long long numel, long long denom,
+                         void* dy, int dy_bf16, float* loss, float grad_scale, void* scratch,
+                         long long scratch_bytes, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Regression head (last Linear with 1..4 outputs, ref.py:44): GEMV + bias + MSE + dY in one kernel,
- * and its backward in one pass over H:  dH = (dY W) * [H > 0] (bf16; pass NULL for the first layer),
+ * and its backward in one pass over H:  dH = (dY W) * [H > 0] (pass NULL for the first layer; H, W, dH are
+ * bf16, or fp32 when elems_fp32 is set - fp32 training),
  * dW = dY^T H, db = sum dY (fp32 or bf16, fixed-order reduction through scratch).
  * scratch: b200dp_head_scratch_bytes(rows, K, nout); first 4 bytes zero before first use.
  */
 long long b200dp_head_scratch_bytes(int rows, int K, int nout);
-int b200dp_head_fwd_mse(const void* H, long long ldh, const void* W, const float* bias, const float* target,
-                        int rows, int K, int nout, float* yhat, float* dy, float* loss, void* scratch,
-                        long long scratch_bytes, void* stream);
-int b200dp_head_bwd(const float* dy, const void* W, const void* H, long long ldh, int rows, int K, int nout,
-                    void* dH, long long lddh, void* dW, void* db, int grads_bf16, void* scratch,
+int b200dp_head_fwd_mse(const void* H, long long ldh, const void* W, int elems_fp32, const float* bias, const float* target,
+                        int rows, int K, int nout, float* yhat, float* dy, float* loss, float grad_scale,
+                        void* scratch, long long scratch_bytes, void* stream);
+/* db_prev (NULL = skip; needs dH): also writes the column sums of dH, i.e. the bias gradient of the
+ * layer below (fused, fixed order) - K values in the gradient dtype. */
+int b200dp_head_bwd(const float* dy, const void* W, const void* H, long long ldh, int elems_fp32, int rows, int K, int nout,
+                    void* dH, long long lddh, void* dW, void* db, void* db_prev, int grads_bf16, void* scratch,
                     long long scratch_bytes, void* stream);
 
 /* Bias gradient of a GEMM layer: out[n] = sum_rows A[r,n]  (the `sum` of AddmmBackward0, ref.py:176). */
 long long b200dp_colsum_scratch_bytes(int rows, int n);
-int b200dp_colsum_bf16(const void* A, long long lda, int rows, int n, void* out, int out_bf16, void* scratch,
-                       long long scratch_bytes, void* stream);
+int b200dp_colsum(const void* A, int a_fp32, long long lda, int rows, int n, void* out, int out_bf16, void* scratch,
+                  long long scratch_bytes, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Local optimizer step, torch.optim.SGD(momentum) semantics (ref.py:91,211):
@@ -144,7 +169,9 @@ int b200dp_gather_rows(const void* src, long long src_row_bytes, const long long
  * gather / root average / send / optimizer.step sequence (ref.py:185-211) as ONE kernel per bucket.
  *   g = (sum_r weights[r]*grads_r) / div  (rank order);  buf = first ? g : mu*buf+g;  p -= lr*buf
  * mode 0 one-shot (every rank reduces everything), 1 two-shot (rank r owns slice r and pushes the
- * updated parameters to all peers), 2 NVLS (multimem.ld_reduce / multimem.st; needs mc_* addresses).
+ * updated parameters to all peers), 2 NVLS (multimem.ld_reduce / multimem.st; needs mc_* addresses;
+ * the switch cannot weight its inputs, so all weights[r] must be equal - pre-scale the gradients).
+ * A peer that does not arrive within timeout_ms sets error_flag and the launch changes nothing.
  * Pointer tables hold every rank's buffer as mapped into THIS process (index `rank` = own buffer).
  * `flags[r]`: rank r's signal pad, B200DP_SYNC_MAX_BLOCKS*B200DP_MAX_RANKS u32, zero-initialised
  * once.  `epochs`: local, B200DP_SYNC_MAX_BLOCKS u32, zero-initialised once.  `error_flag`: local
@@ -171,6 +198,9 @@ typedef struct b200dp_sync_args {
   long long n;                           /* bucket length in elements (multiple of 8) */
   int mode;
   int push_master;                       /* modes 1/2: also write fp32 params into the peers */
+  long long replicate_tail;              /* modes 1/2 without push_master: the last `replicate_tail` elements of the
+                                            bucket (a layer's biases, which kernels read in fp32) still get their
+                                            fp32 value written into every peer; 0 = none */
   int max_blocks;                        /* 0 = one CTA per SM; SM budget of the comm kernel */
   int timeout_ms;                        /* 0 = wait forever */
   const void* mc_grads;                  /* NVLS multicast addresses (mode 2) */

@@ -8,7 +8,12 @@ File layout (``torch.save`` of a dict):
     model      OrderedDict with the reference's keys ``layers.{0,2,...}.{weight,bias}``, fp32 -
                loads straight into the reference's ``MLP`` (ref.py:41-45) / our ``models.MLP``.
     momentum   same keys, the SGD momentum buffers (needed for an exact resume).
-    epoch, step_count, sizes, config, rng (torch CPU generator state), format version.
+    epoch, step_count, sizes, config, format version.
+
+No RNG state is stored: nothing in training draws from a stateful generator.  The initial weights
+come from ``manual_seed(seed)`` once, and the mini-batch permutation of epoch ``e`` on rank ``r`` is a
+pure function of ``(seed, r, e)`` (``data.BatchPlan``), so a run resumed at epoch ``e`` continues the
+exact sequence of the uninterrupted run on every rank.
 """
 from __future__ import annotations
 
@@ -30,7 +35,6 @@ def save_checkpoint(path: str, flat, epoch: int, config: Dict[str, Any], extra: 
         "step_count": int(flat.step_count),
         "sizes": list(flat.spec.logical_sizes),
         "config": dict(config),
-        "rng": torch.random.get_rng_state(),
     }
     if extra:
         payload["extra"] = extra
@@ -56,6 +60,4 @@ def load_checkpoint(path: str, flat, strict_sizes: bool = True) -> Dict[str, Any
     if "momentum" in payload:
         flat.load_momentum_state(payload["momentum"])
     flat.step_count = int(payload.get("step_count", 0))
-    if "rng" in payload:
-        torch.random.set_rng_state(payload["rng"])
     return payload

@@ -196,25 +196,48 @@ def load_validation(cfg) -> Optional[Tuple[torch.Tensor, torch.Tensor]]:
 
 
 class BatchPlan:
-    """Yields ``(row_index_or_None, size)`` per step of an epoch.  Batch == shard (the reference,
-    ref.py:146) gives one step with no permutation (shuffling a full batch is a
-    mathematical no-op); smaller batches draw a fresh seeded permutation per epoch."""
+    """Yields one row index tensor (or ``None`` = the whole shard) per step of an epoch.
 
-    def __init__(self, rows: int, batch: Optional[int], shuffle: bool, seed: int):
-        self.rows, self.shuffle = rows, shuffle
-        self.batch = rows if not batch or batch >= rows else batch
-        self._gen = torch.Generator().manual_seed(seed)
+    Batch == shard (the reference, ref.py:146) gives one step with no permutation (SURVEY Q9:
+    shuffling a full batch is a mathematical no-op).  Smaller batches draw a seeded permutation that
+    is a pure function of ``(seed, epoch)`` - a resumed run continues the sequence exactly - and cut
+    it into ``steps`` nearly equal batches.  Every gradient sync is a collective, so **every rank must
+    run the same number of steps**: ``steps`` is derived from the LARGEST shard
+    (``ceil(max_rows / batch)``), not from this rank's own row count (ref.py:146,155 iterate a
+    per-rank DataLoader; with uneven shards that would give ranks different step counts and hang the
+    collective).  A rank with fewer rows than steps yields empty batches for the remainder: it
+    contributes a zero gradient and keeps the collective in step."""
+
+    def __init__(self, rows: int, batch: Optional[int], shuffle: bool, seed: int,
+                 max_rows: Optional[int] = None):
+        self.rows, self.shuffle, self.seed = rows, shuffle, seed
+        max_rows = rows if max_rows is None else max(int(max_rows), rows)
+        self.full = not batch or batch >= max_rows
+        self.batch = rows if self.full else batch
+        self.steps = (1 if max_rows > 0 else 0) if self.full else -(-max_rows // batch)
+        self.epoch_index = 0
 
     def steps_per_epoch(self) -> int:
-        return 0 if self.rows == 0 else -(-self.rows // self.batch)
+        return self.steps
+
+    def set_epoch(self, epoch: int) -> None:
+        self.epoch_index = int(epoch)
 
     def epoch(self) -> Iterator[Optional[torch.Tensor]]:
-        if self.rows == 0:
+        e = self.epoch_index
+        self.epoch_index += 1
+        if self.rows == 0:                 # the trainer runs this rank's `steps` empty steps itself
             return
-        if self.batch >= self.rows:
-            yield None
+        if self.full:
+            if self.rows > 0:
+                yield None
             return
-        order = torch.randperm(self.rows, generator=self._gen) if self.shuffle \
-            else torch.arange(self.rows)
-        for lo in range(0, self.rows, self.batch):
-            yield order[lo:lo + self.batch]
+        if self.shuffle:
+            gen = torch.Generator().manual_seed((self.seed * 1000003 + e) & 0x7FFFFFFFFFFFFFFF)
+            order = torch.randperm(self.rows, generator=gen)
+        else:
+            order = torch.arange(self.rows)
+        lo = 0
+        for n in shard_counts(self.rows, self.steps):        # first `rows % steps` batches get one more row
+            yield order[lo:lo + n]
+            lo += n

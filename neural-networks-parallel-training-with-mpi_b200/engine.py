@@ -92,7 +92,9 @@ class Trainer:
             self.load_checkpoint(cfg.resume)
 
         batch = cfg.batch_size if cfg.use_batch_size else None
-        self.plan = BatchPlan(self.shard.rows, batch, cfg.shuffle, seed=cfg.seed + 1 + self.rank)
+        self.plan = BatchPlan(self.shard.rows, batch, cfg.shuffle, seed=cfg.seed + 1 + self.rank,
+                              max_rows=max(self.counts))
+        self.plan.set_epoch(self.start_epoch)
         self.x, self.y = self.compute.prepare_batch(self.shard.x.to(self.device),
                                                     self.shard.y.to(self.device))
         if self.world > 1 and self.device.type == "cuda":
@@ -140,6 +142,14 @@ class Trainer:
         if nvtx:
             torch.cuda.nvtx.range_pop()
         return loss
+
+    def _empty_step(self) -> None:
+        """A step of a rank that has no rows for it: zero gradients into the same sync."""
+        begin = getattr(self.sync, "begin_step", None)
+        if begin is not None:
+            begin(self.cfg.lr, self.cfg.momentum)
+        self.flat.grads.zero_()
+        self.sync.sync_and_step(self.flat, self.cfg.lr, self.cfg.momentum)
 
     def _minibatch(self, idx: torch.Tensor):
         """Rows ``idx`` of the resident shard (ref.py:146,155: DataLoader shuffle + collate)."""
@@ -193,18 +203,22 @@ class Trainer:
             emit(epoch_banner(epoch), cfg.quiet)                                # ref.py:152
             t0 = time.perf_counter()
             loss = None
+            self.plan.set_epoch(epoch)
             for idx in self.plan.epoch():                                       # ref.py:155
+                if idx is not None and idx.numel() == 0:
+                    # this rank has run out of rows while a larger shard still has a batch: a zero
+                    # gradient keeps the collective in step (every rank syncs once per step)
+                    self._empty_step()
+                    continue
                 xb, yb = (self.x, self.y) if idx is None else self._minibatch(idx)
                 loss = self.graph_step() if (use_graph and idx is None) else self.step(xb, yb)
-            if loss is None:                                                    # rank owns no rows
-                self.flat.grads.zero_()
-                self.sync.sync_and_step(self.flat, cfg.lr, cfg.momentum)
-                loss_val = float("nan")
-            else:
-                loss_val = float(loss.item())                                   # ref.py:224
-                check = getattr(self.sync, "check_errors", None)
-                if check is not None:
-                    check()                                                     # watchdog
+            if self.shard.rows == 0:                                            # rank owns no rows at all
+                for _ in range(self.plan.steps_per_epoch()):
+                    self._empty_step()
+            loss_val = float("nan") if loss is None else float(loss.item())     # ref.py:224
+            check = getattr(self.sync, "check_errors", None)
+            if check is not None:
+                check()                                                         # watchdog
             emit(loss_line(self.rank, loss_val), cfg.quiet)
             rec = {"epoch": epoch, "rank": self.rank, "loss": loss_val,
                    "epoch_s": time.perf_counter() - t0}
@@ -322,6 +336,9 @@ class Trainer:
         return self.flat.state_dict()
 
     def save_checkpoint(self, path: str, epoch: int) -> None:
+        check = getattr(self.sync, "check_errors", None)
+        if check is not None:
+            check()                              # never persist parameters a timed-out sync left behind
         if self._runtime is not None:
             self._runtime.gather_optimizer_state()
         if self.rank == 0:

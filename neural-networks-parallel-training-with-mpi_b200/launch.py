@@ -10,7 +10,7 @@ from __future__ import annotations
 
 import os
 from dataclasses import dataclass
-from typing import Mapping, Optional
+from typing import List, Mapping, Optional
 
 
 @dataclass(frozen=True)
@@ -52,13 +52,93 @@ def discover(env: Optional[Mapping[str, str]] = None) -> RankInfo:
     return RankInfo(0, 1, 0, "single", addr, port)
 
 
+def pcie_closeness() -> Optional[List[List[int]]]:
+    """``c[i][j]`` = how much of the PCIe path to the host the visible GPUs i and j share (larger =
+    closer = more contention for host copies).  NVLink says nothing about this: on an HGX board every
+    pair is NV18, yet pairs of GPUs hang off one PCIe switch and share its x16 uplink - two ranks that
+    feed batches from host memory through the same uplink each get half of it.  Source: NVML's common
+    ancestor level (PIX/PXB = same switch), else the sysfs device paths; ``None`` if neither is
+    available."""
+    try:
+        import pynvml
+        import torch
+        n = torch.cuda.device_count()
+        pynvml.nvmlInit()
+        hs = [pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + str(torch.cuda.get_device_properties(i).uuid)).encode())
+              for i in range(n)]
+    except Exception:
+        return None
+    score = [[0] * n for _ in range(n)]
+    ok = False
+    try:
+        # NVML_TOPOLOGY_INTERNAL 0, SINGLE 10, MULTIPLE 20, HOSTBRIDGE 30, NODE 40, SYSTEM 50
+        for i in range(n):
+            for j in range(i + 1, n):
+                lvl = int(pynvml.nvmlDeviceGetTopologyCommonAncestor(hs[i], hs[j]))
+                score[i][j] = score[j][i] = 60 - lvl
+        ok = len({score[i][j] for i in range(n) for j in range(n) if i != j}) > 1
+    except Exception:
+        ok = False
+    if not ok:
+        try:        # sysfs: number of shared path components below the PCI root
+            paths = []
+            for h in hs:
+                bus = pynvml.nvmlDeviceGetPciInfo(h).busId
+                bus = bus.decode() if isinstance(bus, bytes) else bus
+                name = bus.lower()[-12:]                      # 00000000:1B:00.0 -> 0000:1b:00.0
+                paths.append(os.path.realpath(f"/sys/bus/pci/devices/{name}").split("/"))
+            for i in range(n):
+                for j in range(i + 1, n):
+                    k = 0
+                    while k < min(len(paths[i]), len(paths[j])) and paths[i][k] == paths[j][k]:
+                        k += 1
+                    score[i][j] = score[j][i] = k
+            ok = len({score[i][j] for i in range(n) for j in range(n) if i != j}) > 1
+        except Exception:
+            ok = False
+    return score if ok else None
+
+
+def spread_devices(count: int, closeness: Optional[List[List[int]]], n_visible: int) -> List[int]:
+    """``count`` of the ``n_visible`` GPUs, chosen greedily so that the closest pair among them is as
+    far apart on PCIe as possible (one GPU per switch before any switch gets a second one).
+    Deterministic: every rank computes the same list.  Without topology data: 0, 1, 2, ..."""
+    count = min(count, n_visible)
+    if closeness is None or count >= n_visible:
+        return list(range(count))
+    chosen = [0]
+    while len(chosen) < count:
+        best, best_key = None, None
+        for d in range(n_visible):
+            if d in chosen:
+                continue
+            key = (max(closeness[d][c] for c in chosen), sum(closeness[d][c] for c in chosen), d)
+            if best_key is None or key < best_key:
+                best, best_key = d, key
+        chosen.append(best)
+    return chosen
+
+
+def device_index_for(local_rank: int, local_world: Optional[int] = None) -> int:
+    """GPU index for this rank.  When the job uses fewer GPUs than are visible (a 2- or 4-rank run on
+    an 8-GPU box) the ranks are spread over distinct PCIe uplinks instead of taking GPUs 0..N-1."""
+    import torch
+
+    n = torch.cuda.device_count()
+    if local_world is None:
+        local_world = _first_int(os.environ, "LOCAL_WORLD_SIZE", "OMPI_COMM_WORLD_LOCAL_SIZE", "WORLD_SIZE") or 1
+    if os.environ.get("B200DP_PLACEMENT", "spread") != "spread" or local_world >= n or local_world < 1:
+        return local_rank % max(n, 1)
+    devs = spread_devices(local_world, pcie_closeness(), n)
+    return devs[local_rank % len(devs)]
+
+
 def bind_device(info: RankInfo):
-    """Returns the torch.device this rank drives (cuda:LOCAL_RANK, or cpu when there is no GPU)."""
+    """Returns the torch.device this rank drives (one GPU per process, or cpu when there is no GPU)."""
     import torch
 
     if torch.cuda.is_available():
-        n = torch.cuda.device_count()
-        dev = info.local_rank % max(n, 1)
+        dev = device_index_for(info.local_rank)
         torch.cuda.set_device(dev)
         bind_cpu_near_gpu(dev)
         return torch.device("cuda", dev)

@@ -64,12 +64,13 @@ class MLPSpec:
     gradients are identically zero) and never appear in ``state_dict``.  ``sizes`` are the physical
     (padded) widths the kernels see, ``logical_sizes`` the model's own."""
 
-    def __init__(self, sizes: Sequence[int], pad_to: int = 1):
+    def __init__(self, sizes: Sequence[int], pad_to: int = 1, pad_last: bool = False):
         if len(sizes) < 2:
             raise ValueError("an MLP needs at least an input and an output size")
         self.logical_sizes = tuple(int(s) for s in sizes)
         self.pad_to = int(pad_to)
-        self.sizes = tuple(_round_up(s, self.pad_to) if i < len(sizes) - 1 else s
+        self.pad_last = bool(pad_last)     # also round the output width up (GEMM head with 5-7, 9-15, ... outputs)
+        self.sizes = tuple(_round_up(s, self.pad_to) if (i < len(sizes) - 1 or pad_last) else s
                            for i, s in enumerate(self.logical_sizes))
         self.num_layers = len(self.sizes) - 1
         segs: List[Segment] = []
@@ -205,11 +206,21 @@ class FlatMLP:
         return m
 
     def fingerprint(self) -> int:
-        """Order-sensitive 64-bit hash of the bytes every replica computes with (replica-equality
-        checks): the bf16 shadow weights in bf16 mode - the fp32 master of a slice may live only on
-        its owner rank there - else the fp32 parameters."""
-        src = self.shadow if self.shadow is not None else self.params
-        b = src.detach().to("cpu").contiguous().view(torch.uint8).numpy().tobytes()
+        """Order-sensitive 64-bit hash of every byte a kernel computes with (replica-equality
+        checks).  fp32 mode: the fp32 parameters.  bf16 mode: the bf16 shadow weights AND the fp32
+        biases (the GEMM / head epilogues read those from the master buffer); the rest of the fp32
+        master is left out because a slice of it may live only on its owner rank."""
         import hashlib
 
-        return int.from_bytes(hashlib.blake2b(b, digest_size=8).digest(), "little")
+        h = hashlib.blake2b(digest_size=8)
+
+        def feed(t: torch.Tensor) -> None:
+            h.update(t.detach().to("cpu").contiguous().view(torch.uint8).numpy().tobytes())
+
+        if self.shadow is None:
+            feed(self.params)
+        else:
+            feed(self.shadow)
+            for l in range(self.spec.num_layers):
+                feed(self.bias(l))
+        return int.from_bytes(h.digest(), "little")

@@ -28,7 +28,9 @@ class GemmArgs(C.Structure):
         ("D", c_void_p), ("ldd", c_ll), ("d_fp32", c_int),
         ("bias", c_void_p), ("relu", c_int),
         ("mask_src", c_void_p), ("ldmask", c_ll),
-        ("tile_n", c_int), ("max_ctas", c_int), ("cta_group", c_int),
+        ("tile_n", c_int), ("max_ctas", c_int), ("cta_group", c_int), ("split_tail", c_int),
+        ("colsum_out", c_void_p), ("colsum_out_bf16", c_int),
+        ("colsum_scratch", c_void_p), ("colsum_scratch_bytes", c_ll),
     ]
 
 
@@ -40,6 +42,9 @@ def _declare(lib: C.CDLL) -> None:
     lib.b200dp_last_error.restype = C.c_char_p
     lib.b200dp_version.restype = c_int
     lib.b200dp_gemm_bf16.argtypes = [C.POINTER(GemmArgs), c_void_p]
+    lib.b200dp_gemm_tf32.argtypes = [C.POINTER(GemmArgs), c_void_p]
+    lib.b200dp_gemm_colsum_scratch_bytes.argtypes = [c_int, c_int]
+    lib.b200dp_gemm_colsum_scratch_bytes.restype = c_ll
     for name, argtypes in _SIGNATURES.items():
         fn = getattr(lib, name, None)
         if fn is not None:

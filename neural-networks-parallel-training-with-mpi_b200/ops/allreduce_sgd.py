@@ -22,7 +22,7 @@ class SyncArgs(C.Structure):
         ("momentum", c_void_p), ("epochs", c_void_p), ("error_flag", c_void_p),
         ("weights", c_float * MAX_RANKS), ("div", c_float), ("lr", c_float), ("mu", c_float),
         ("first_step", c_int), ("grads_bf16", c_int), ("offset", c_ll), ("n", c_ll),
-        ("mode", c_int), ("push_master", c_int), ("max_blocks", c_int), ("timeout_ms", c_int),
+        ("mode", c_int), ("push_master", c_int), ("replicate_tail", c_ll), ("max_blocks", c_int), ("timeout_ms", c_int),
         ("mc_grads", c_void_p), ("mc_shadow", c_void_p), ("mc_params", c_void_p),
     ]
 
@@ -52,17 +52,23 @@ def make_args(rank: int, world: int, grads: Sequence[int], params: Sequence[int]
     return a
 
 
-def launch(a: SyncArgs, offset: int, n: int, lr: float, mu: float, first_step: bool, stream=None) -> None:
+def launch(a: SyncArgs, offset: int, n: int, lr: float, mu: float, first_step: bool, stream=None,
+           replicate_tail: int = 0) -> None:
+    """``replicate_tail``: the last that-many elements of the bucket (a layer's biases) get their fp32
+    master value written into every peer even when the master is otherwise sharded (bf16 two-shot /
+    NVLS), because kernels read them in fp32 on every rank."""
     a.offset, a.n, a.lr, a.mu, a.first_step = offset, n, lr, mu, int(first_step)
+    a.replicate_tail = replicate_tail
     _lib.check(_lib.lib().b200dp_allreduce_sgd(C.byref(a), _lib.stream_ptr(stream)))
     _lib.count()
 
 
 def launch_emulated(per_rank: List[SyncArgs], offset: int, n: int, lr: float, mu: float, first_step: bool,
-                    device_args: torch.Tensor, stream=None) -> None:
+                    device_args: torch.Tensor, stream=None, replicate_tail: int = 0) -> None:
     arr = (SyncArgs * len(per_rank))()
     for i, a in enumerate(per_rank):
         a.offset, a.n, a.lr, a.mu, a.first_step = offset, n, lr, mu, int(first_step)
+        a.replicate_tail = replicate_tail
         C.memmove(C.byref(arr, i * C.sizeof(SyncArgs)), C.byref(a), C.sizeof(SyncArgs))
     _lib.check(_lib.lib().b200dp_allreduce_sgd_emulated(arr, len(per_rank), device_args.data_ptr(),
                                                         _lib.stream_ptr(stream)))

@@ -75,67 +75,76 @@ class TinyCompute:
 
 # =============================================================================== compute: gemm
 class GemmCompute:
-    """bf16 tensor-core path: tcgen05 GEMMs + fused head/MSE kernels."""
+    """Tensor-core path: tcgen05 GEMMs + fused head/MSE kernels.  bf16 training runs ``kind::f16`` on
+    the bf16 shadow weights (fp32 master kept by the optimizer); fp32 training - the reference's own
+    precision, ref.py:159 - runs ``kind::tf32`` straight on the fp32 parameters."""
     name = "cuda-tcgen05"
 
     def __init__(self, flat: FlatMLP, max_rows: int):
         spec = flat.spec
-        if flat.shadow is None:
-            raise ValueError("the tensor-core path trains in bf16 (use --dtype bf16)")
         for s in spec.sizes[:-1]:
             if s % 8:
                 raise ValueError(f"tensor-core path needs physical widths that are multiples of 8 (got {s}); "
                                  "build the spec with MLPSpec(sizes, pad_to=8)")
-        self.nout = spec.sizes[-1]
+        self.nout = spec.sizes[-1]                    # physical outputs (padded to 8 when 5-7, 9-15, ...)
+        self.nout_logical = spec.logical_sizes[-1]
         if self.nout > 4 and self.nout % 8:
-            raise ValueError("n_outputs must be <= 4 (fused GEMV head) or a multiple of 8 (GEMM head)")
+            raise ValueError("the GEMM head needs a multiple of 8 outputs: build the spec with "
+                             "MLPSpec(sizes, pad_to=8, pad_last=True)")
         self.flat, self.spec, self.L = flat, spec, spec.num_layers
         dev = flat.device
         R = max(max_rows, 1)
         self.max_rows = R
-        bf = torch.bfloat16
+        self.cdt = cdt = torch.bfloat16 if flat.shadow is not None else torch.float32
         # activations a[l] = input of layer l (a[0] is the batch itself); d[l] = dLoss/da[l]
         self.acts: List[Optional[torch.Tensor]] = [None] + [
-            torch.empty(R, spec.sizes[l], dtype=bf, device=dev) for l in range(1, self.L)]
+            torch.empty(R, spec.sizes[l], dtype=cdt, device=dev) for l in range(1, self.L)]
         hid = max(spec.sizes[1:self.L], default=8)
-        self.dbuf = [torch.empty(R * hid, dtype=bf, device=dev) for _ in range(2)]
+        self.dbuf = [torch.empty(R * hid, dtype=cdt, device=dev) for _ in range(2)]
         self.loss = torch.zeros((), dtype=torch.float32, device=dev)
         self.head_is_gemv = self.nout <= 4
+        self.yhat = torch.empty(R, self.nout, dtype=torch.float32, device=dev)
         if self.head_is_gemv:
-            self.yhat = torch.empty(R, self.nout, dtype=torch.float32, device=dev)
             self.dy32 = torch.empty(R, self.nout, dtype=torch.float32, device=dev)
             self.head_scratch = K.scratch(K.head_scratch_bytes(R, spec.sizes[self.L - 1], self.nout), dev)
         else:
-            self.yhat = torch.empty(R, self.nout, dtype=torch.float32, device=dev)   # fp32 logits
-            self.dyb = torch.empty(R, self.nout, dtype=bf, device=dev)
+            self.dyb = torch.empty(R, self.nout, dtype=cdt, device=dev)
             self.mse_scratch = K.scratch(K.mse_scratch_bytes(R * self.nout), dev)
+            self.colsum_scratch = K.scratch(K.colsum_scratch_bytes(R, self.nout), dev)
+        # fused bias gradients: the GEMM that produces dY_l also reduces its columns (tickets + partials)
         widest = max(spec.sizes[1:])
-        self.colsum_scratch = K.scratch(K.colsum_scratch_bytes(R, _align(widest, 8)), dev)
+        self.gemm_cs_scratch = K.scratch(gemm.colsum_scratch_bytes(R, widest), dev)
         self.bucket_hook: Optional[Callable[..., None]] = None
         self.wgrad_chunks = {}            # layer -> [(row0, row1), ...] of its weight (set with the buckets)
-        self.aux_stream = None            # side stream shared with the sync strategy (bias-grad column sums)
-        self._ev_dy = torch.cuda.Event()
-        self._ev_colsum = [torch.cuda.Event(), torch.cuda.Event()]
-        self._colsum_pending = [False, False]
+        self.aux_stream = None            # side stream of the sync strategy (unused by the compute path now)
         self.gemm_max_ctas = 0
+        self.grad_scale = 1.0             # this rank's weight in the all-reduce, folded into dLoss/dYhat
+        self._zero_targets = None
 
     def prepare_batch(self, x, y):
         k_phys = self.spec.sizes[0]
+        y = y.to(torch.float32)
+        if y.shape[1] != self.nout:                    # padded head: zero targets for the padding outputs
+            yp = torch.zeros(y.shape[0], self.nout, dtype=torch.float32, device=y.device)
+            yp[:, :y.shape[1]].copy_(y)
+            y = yp
         if x.shape[1] != k_phys:                       # padded input width: zero columns on the right
-            xb = torch.zeros(x.shape[0], k_phys, dtype=torch.bfloat16, device=x.device)
+            xb = torch.zeros(x.shape[0], k_phys, dtype=self.cdt, device=x.device)
             xb[:, :x.shape[1]].copy_(x)
-            return xb, y.to(torch.float32).contiguous()
+            return xb, y.contiguous()
+        if self.cdt == torch.float32:
+            return x.to(torch.float32).contiguous(), y.contiguous()
         xb = torch.empty(x.shape, dtype=torch.bfloat16, device=x.device)
         if x.numel():
             if x.dtype == torch.bfloat16:
                 xb.copy_(x)
             else:
                 K.cast_f32_bf16(x.to(torch.float32).contiguous(), xb)
-        return xb, y.to(torch.float32).contiguous()
+        return xb, y.contiguous()
 
     # ---- views ----
     def _w(self, l):
-        return self.flat.weight(l, self.flat.shadow)
+        return self.flat.compute_weight(l)
 
     def _gw(self, l):
         return self.flat.weight(l, self.flat.grads)
@@ -155,6 +164,12 @@ class GemmCompute:
             h = out
         return h
 
+    def _dgrad(self, dy, l, a_in, out) -> None:
+        """dLoss/d(input of layer l) with the ReLU mask of that input, and - fused into the epilogue -
+        its column sums = the bias gradient of layer l-1 (the `sum` of AddmmBackward0, ref.py:176)."""
+        gemm.linear_dgrad(dy, self._w(l), a_in, out=out, max_ctas=self.gemm_max_ctas,
+                          colsum_out=self._gb(l - 1), colsum_scratch=self.gemm_cs_scratch)
+
     def loss_and_grads(self, x, y) -> torch.Tensor:
         rows = x.shape[0]
         if rows == 0:
@@ -165,47 +180,46 @@ class GemmCompute:
                     self.bucket_hook(l)
             return self.loss
         L, flat = self.L, self.flat
-        # every side-stream event of the previous step completed before that step ended (the streams are
-        # joined in sync_and_step); never wait on an event from before this step (or from before a
-        # CUDA-graph capture began)
-        self._colsum_pending = [False, False]
         h = self.forward_hidden(x)
         last = L - 1
         # ---- head forward + loss + dY, head backward ----
+        dnext = None
         if self.head_is_gemv:
             yhat, dy = self.yhat[:rows], self.dy32[:rows]
-            K.head_fwd_mse(h, self._w(last), flat.bias(last), y, yhat, dy, self.loss, self.head_scratch)
-            dnext = self._d(last, rows, self.spec.sizes[last]) if last > 0 else None
-            K.head_bwd(dy, self._w(last), h, dnext, self._gw(last), self._gb(last), self.head_scratch)
+            K.head_fwd_mse(h, self._w(last), flat.bias(last), y, yhat, dy, self.loss, self.head_scratch,
+                           grad_scale=self.grad_scale)
+            if last > 0:
+                dnext = self._d(last, rows, self.spec.sizes[last])
+            K.head_bwd(dy, self._w(last), h, dnext, self._gw(last), self._gb(last), self.head_scratch,
+                       db_prev=self._gb(last - 1) if last > 0 else None)
+            if self.bucket_hook is not None:
+                self.bucket_hook(last)
         else:
             yhat, dy = self.yhat[:rows], self.dyb[:rows]
             gemm.linear_fwd(h, self._w(last), flat.bias(last), relu=False, out=yhat, max_ctas=self.gemm_max_ctas)
-            K.mse_loss_grad(yhat, y, dy, self.loss, self.mse_scratch)
-            self._bias_grad(dy, last)
-            dnext = None
+            # padded outputs predict 0 against a 0 target: they add nothing, the mean is over real outputs
+            K.mse_loss_grad(yhat, y, dy, self.loss, self.mse_scratch, grad_scale=self.grad_scale,
+                            denom=rows * self.nout_logical)
+            K.colsum(dy, self._gb(last), self.colsum_scratch)
             if last > 0:
                 dnext = self._d(last, rows, self.spec.sizes[last])
-                gemm.linear_dgrad(dy, self._w(last), h, out=dnext, max_ctas=self.gemm_max_ctas)
+                self._dgrad(dy, last, h, dnext)
             self._wgrad_chunked(dy, h, last)
-        if self.head_is_gemv and self.bucket_hook is not None:
-            self.bucket_hook(last)
         # ---- hidden layers, top down ----
         for l in range(L - 2, -1, -1):
             dy_l = dnext                                   # dLoss/d(pre-activation of layer l), [rows, sizes[l+1]]
             a_in = x if l == 0 else self.acts[l][:rows]
-            self._bias_grad(dy_l, l)
             if l > 0:
                 # dgrad first: it is on the critical path of backward, and it must have read W_l
                 # before the first chunk of this layer's sync is allowed to update W_l
                 dnext = self._d(l, rows, self.spec.sizes[l])
-                self._wait_bias_grad(l)
-                gemm.linear_dgrad(dy_l, self._w(l), a_in, out=dnext, max_ctas=self.gemm_max_ctas)
+                self._dgrad(dy_l, l, a_in, dnext)
             self._wgrad_chunked(dy_l, a_in, l)
         return self.loss
 
     def _wgrad_chunked(self, dy, a_in, l) -> None:
         """dW_l = dY^T a_in, one GEMM per row chunk of W_l; each chunk's bucket is handed to the sync
-        strategy as soon as its GEMM is queued."""
+        strategy as soon as its GEMM is queued.  (db_l was written by the kernel that produced dY.)"""
         gw = self._gw(l)
         chunks = self.wgrad_chunks.get(l) or [(0, gw.shape[0])]
         for c, (r0, r1) in enumerate(chunks):
@@ -216,39 +230,29 @@ class GemmCompute:
             if self.bucket_hook is not None:
                 self.bucket_hook(l, c)
 
-    def _bias_grad(self, dy, l) -> None:
-        """db_l = column sums of dY_l.  HBM-bound and independent of the GEMMs that follow, so it
-        runs on the side stream (ordered before that layer's sync kernel, which is queued there)."""
-        aux = self.aux_stream
-        if aux is None:
-            K.colsum(dy, self._gb(l), self.colsum_scratch)
-            return
-        main = torch.cuda.current_stream()
-        self._ev_dy.record(main)
-        aux.wait_event(self._ev_dy)
-        K.colsum(dy, self._gb(l), self.colsum_scratch, stream=aux)
-        self._ev_colsum[l & 1].record(aux)
-        self._colsum_pending[l & 1] = True
-
-    def _wait_bias_grad(self, l: int) -> None:
-        """The d-buffers ping-pong: dgrad of layer l writes the buffer that the column-sum of layer
-        l+1 (queued a whole layer earlier on the side stream) has been reading.  Wait for THAT one -
-        not for layer l's own column-sum, which would put it on the critical path."""
-        k = (l + 1) & 1
-        if self.aux_stream is not None and self._colsum_pending[k]:
-            torch.cuda.current_stream().wait_event(self._ev_colsum[k])
-            self._colsum_pending[k] = False
-
     @torch.no_grad()
     def predict(self, x) -> torch.Tensor:
-        xb, _ = self.prepare_batch(x, torch.zeros(x.shape[0], self.nout, device=x.device))
-        rows = xb.shape[0]
+        """Forward only, on the same kernels as training (the reference's dead eval stubs,
+        ref.py:213-236)."""
+        rows = x.shape[0]
         if rows > self.max_rows:
             return torch.cat([self.predict(x[i:i + self.max_rows]) for i in range(0, rows, self.max_rows)])
+        if rows == 0:
+            return torch.empty(0, self.nout_logical, dtype=torch.float32, device=x.device)
+        if self._zero_targets is None:
+            self._zero_targets = torch.zeros(self.max_rows, self.nout, dtype=torch.float32, device=x.device)
+        xb, _ = self.prepare_batch(x, self._zero_targets[:rows])
         h = self.forward_hidden(xb)
         last = self.L - 1
-        w, b = self._w(last), self.flat.bias(last)
-        return h.float() @ w.float().t() + b        # evaluation only, off the training path
+        yhat = torch.empty(rows, self.nout, dtype=torch.float32, device=x.device)
+        if self.head_is_gemv:
+            loss = torch.empty((), dtype=torch.float32, device=x.device)
+            K.head_fwd_mse(h, self._w(last), self.flat.bias(last), self._zero_targets[:rows], yhat,
+                           self.dy32[:rows], loss, self.head_scratch)
+        else:
+            gemm.linear_fwd(h, self._w(last), self.flat.bias(last), relu=False, out=yhat,
+                            max_ctas=self.gemm_max_ctas)
+        return yhat[:, :self.nout_logical]
 
 
 # =============================================================================== sync strategies
@@ -337,6 +341,7 @@ class BucketedSync(GradSync):
         self._done = torch.cuda.Event()
         self._launched = set()
         self._lr = self._mu = None
+        self._prof = None
         self._by_key = {(b.layer, b.chunk): i for i, b in enumerate(buckets)}
         self.chunks_of = {}
         for b in buckets:
@@ -360,17 +365,45 @@ class BucketedSync(GradSync):
         if i in self._launched:
             return
         main = torch.cuda.current_stream()
+        stream = main
         if self.comm_stream is not None:
             self._ready.record(main)
             self.comm_stream.wait_event(self._ready)
-            self._run_bucket(self.buckets[i], self._lr, self._mu, self.comm_stream)
+            stream = self.comm_stream
+        if self._prof is not None:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            self._run_bucket(self.buckets[i], self._lr, self._mu, stream)
+            e1.record(stream)
+            self._prof[-1]["buckets"].append((e0, e1))
         else:
-            self._run_bucket(self.buckets[i], self._lr, self._mu, main)
+            self._run_bucket(self.buckets[i], self._lr, self._mu, stream)
         self._launched.add(i)
+
+    # ---- "grad-sync us/step" (BASELINE.json metric) ----
+    def start_profile(self) -> None:
+        """From now on every step records CUDA events around each bucket's sync kernel and around the
+        main stream's final wait for the side stream."""
+        self._prof = []
+
+    def stop_profile(self):
+        """Per profiled step: ``busy_us`` = summed device time of the sync(+update) kernels,
+        ``exposed_us`` = how long the main stream sat in the final join after its own last kernel
+        (the part of the sync that backward did not hide)."""
+        torch.cuda.synchronize()
+        out = []
+        for st in self._prof or []:
+            busy = sum(a.elapsed_time(b) for a, b in st["buckets"]) * 1e3
+            exposed = st["tail0"].elapsed_time(st["tail1"]) * 1e3 if "tail0" in st else busy
+            out.append({"busy_us": busy, "exposed_us": exposed, "kernels": len(st["buckets"])})
+        self._prof = None
+        return out
 
     def begin_step(self, lr: float, mu: float) -> None:
         self._lr, self._mu = lr, mu
         self._launched.clear()
+        if self._prof is not None:
+            self._prof.append({"buckets": []})
 
     def sync_and_step(self, flat, lr, mu):
         if self._lr is None:
@@ -378,8 +411,16 @@ class BucketedSync(GradSync):
         for i in range(len(self.buckets)):
             self._launch(i)
         if self.comm_stream is not None:
+            main = torch.cuda.current_stream()
             self._done.record(self.comm_stream)
-            torch.cuda.current_stream().wait_event(self._done)
+            if self._prof is not None:
+                t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                t0.record(main)
+                main.wait_event(self._done)
+                t1.record(main)
+                self._prof[-1]["tail0"], self._prof[-1]["tail1"] = t0, t1
+            else:
+                main.wait_event(self._done)
         self._lr = None
         flat.step_count += 1
 
@@ -460,8 +501,16 @@ class FusedSync(BucketedSync):
             symm.mc("grads"), symm.mc("shadow") if flat.shadow is not None else None, symm.mc("params"))
         self.sharded_master = (m != 0) and not self.push_master
 
+        # kernels read the biases in fp32 from the master buffer: when the master is sharded, the part
+        # of a bucket from its layer's bias onwards is still written into every rank
+        self._tail = {}
+        for i, b in enumerate(buckets):
+            bias_off = flat.spec.layer_segments(b.layer)[1].offset
+            self._tail[(b.start, b.stop)] = max(0, b.stop - max(b.start, bias_off)) if self.sharded_master else 0
+
     def _run_bucket(self, b, lr, mu, stream):
-        ar.launch(self.args, b.start, b.stop - b.start, lr, mu, False, stream=stream)
+        ar.launch(self.args, b.start, b.stop - b.start, lr, mu, False, stream=stream,
+                  replicate_tail=self._tail[(b.start, b.stop)])
 
     def calibrate(self, modes, iters: int = 4) -> str:
         """Start-up pick between sync variants: times each on the largest bucket (device-timed, max
@@ -537,13 +586,14 @@ class CudaRuntime:
         spec: MLPSpec = trainer.spec
         self.comm, self.cfg = comm, cfg
         tiny = is_tiny(spec) and cfg.dtype == "fp32"
-        if not tiny and any(s % 8 for s in spec.sizes[:-1]):
-            # tensor-core path: rows must be whole 16-byte vectors -> pad widths to multiples of 8
-            spec = MLPSpec(spec.logical_sizes, pad_to=8)
-            trainer.spec = spec
-        if not tiny and cfg.dtype != "bf16":
-            raise ValueError("models beyond the fused SIMT kernel's size train on the tensor-core path: "
-                             "pass --dtype bf16")
+        if not tiny:
+            # tensor-core path: rows must be whole 16-byte vectors -> pad widths to multiples of 8; a
+            # head with 5-7, 9-15, ... outputs is padded too (<= 4 outputs take the fused GEMV head)
+            nout = spec.logical_sizes[-1]
+            pad_last = nout > 4 and nout % 8 != 0
+            if pad_last or any(s_ % 8 for s_ in spec.sizes[:-1]):
+                spec = MLPSpec(spec.logical_sizes, pad_to=8, pad_last=pad_last)
+                trainer.spec = spec
         sync_name = cfg.sync
         auto = sync_name == "auto"
         if auto:
@@ -557,6 +607,19 @@ class CudaRuntime:
                     sync_name = "fused_oneshot"
         fused = comm.size > 1 and sync_name.startswith("fused")
         weights, divisor = weights_and_divisor(trainer.counts, cfg.grad_weighting)
+        uniform = all(w == weights[0] for w in weights)
+        # Non-uniform per-rank weights (sample weighting of uneven shards): on the tensor-core
+        # path every rank folds its weight into dLoss/dYhat, so its gradients arrive pre-weighted and any
+        # reduction - the NVSwitch's plain sum included - gives sum_r w_r g_r.  The SIMT path keeps the
+        # weights inside the peer-load kernels (one-/two-shot); it never takes NVLS with unequal weights.
+        prescale = fused and not tiny and not uniform
+        my_weight = weights[comm.rank]
+        if prescale:
+            weights = [1.0] * comm.size
+        if fused and tiny and not uniform and sync_name == "fused_nvls":
+            if comm.rank == 0 and not auto:
+                print("b200dp: NVLS cannot weight its inputs - using fused_twoshot for the sample-weighted sync")
+            sync_name = "fused_twoshot"
         self.symm: Optional[SymmLayout] = None
         grads_bf16 = cfg.dtype == "bf16"
         if fused:
@@ -575,6 +638,8 @@ class CudaRuntime:
             self.flat = FlatMLP(spec, dev, cfg.dtype)
         max_rows = trainer.shard.rows
         self.compute = TinyCompute(self.flat, max_rows) if tiny else GemmCompute(self.flat, max_rows)
+        if prescale:
+            self.compute.grad_scale = float(my_weight)
         self.buckets = make_buckets(spec, cfg.bucket_mb, 2 if grads_bf16 else 4,
                                     units=max(torch.cuda.get_device_properties(dev).multi_processor_count // 2, 1))
         if tiny:

@@ -19,13 +19,13 @@ class MlpDesc(C.Structure):
 
 _lib.register("b200dp_tiny_mlp_fwd_bwd", [C.POINTER(MlpDesc), c_void_p, c_void_p, c_void_p, c_int, c_void_p,
                                           c_void_p, c_void_p, c_ll, c_void_p])
-_lib.register("b200dp_mse_loss_grad", [c_void_p, c_int, c_void_p, c_ll, c_void_p, c_int, c_void_p, c_void_p,
-                                       c_ll, c_void_p])
-_lib.register("b200dp_head_fwd_mse", [c_void_p, c_ll, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
-                                      c_void_p, c_void_p, c_void_p, c_void_p, c_ll, c_void_p])
-_lib.register("b200dp_head_bwd", [c_void_p, c_void_p, c_void_p, c_ll, c_int, c_int, c_int, c_void_p, c_ll,
-                                  c_void_p, c_void_p, c_int, c_void_p, c_ll, c_void_p])
-_lib.register("b200dp_colsum_bf16", [c_void_p, c_ll, c_int, c_int, c_void_p, c_int, c_void_p, c_ll, c_void_p])
+_lib.register("b200dp_mse_loss_grad", [c_void_p, c_int, c_void_p, c_ll, c_ll, c_void_p, c_int, c_void_p, c_float,
+                                       c_void_p, c_ll, c_void_p])
+_lib.register("b200dp_head_fwd_mse", [c_void_p, c_ll, c_void_p, c_int, c_void_p, c_void_p, c_int, c_int, c_int,
+                                      c_void_p, c_void_p, c_void_p, c_float, c_void_p, c_ll, c_void_p])
+_lib.register("b200dp_head_bwd", [c_void_p, c_void_p, c_void_p, c_ll, c_int, c_int, c_int, c_int, c_void_p, c_ll,
+                                  c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_ll, c_void_p])
+_lib.register("b200dp_colsum", [c_void_p, c_int, c_ll, c_int, c_int, c_void_p, c_int, c_void_p, c_ll, c_void_p])
 _lib.register("b200dp_sgd_momentum", [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_ll, c_float, c_float,
                                       c_float, c_int, c_void_p])
 _lib.register("b200dp_sgd_momentum_ex", [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_ll, c_float, c_float,
@@ -91,12 +91,14 @@ def mse_scratch_bytes(numel: int) -> int:
     return int(L().b200dp_mse_scratch_bytes(numel))
 
 
-def mse_loss_grad(pred, target, dy, loss, scratch_buf, stream=None):
+def mse_loss_grad(pred, target, dy, loss, scratch_buf, stream=None, grad_scale: float = 1.0, denom: int = 0):
+    """``loss = sum((pred-target)^2) / n``, ``dy = grad_scale * 2 (pred-target) / n``; ``n = denom`` when
+    given (padded outputs), else ``numel``."""
     assert pred.is_contiguous() and target.is_contiguous() and dy.is_contiguous()
     assert target.dtype == torch.float32 and pred.numel() == target.numel() == dy.numel()
     _lib.check(L().b200dp_mse_loss_grad(pred.data_ptr(), int(pred.dtype == torch.bfloat16), target.data_ptr(),
-                                        pred.numel(), dy.data_ptr(), int(dy.dtype == torch.bfloat16),
-                                        loss.data_ptr(), scratch_buf.data_ptr(), scratch_buf.numel(),
+                                        pred.numel(), denom, dy.data_ptr(), int(dy.dtype == torch.bfloat16),
+                                        loss.data_ptr(), grad_scale, scratch_buf.data_ptr(), scratch_buf.numel(),
                                         _lib.stream_ptr(stream)))
     _lib.count()
 
@@ -105,23 +107,31 @@ def head_scratch_bytes(rows: int, K: int, nout: int) -> int:
     return int(L().b200dp_head_scratch_bytes(rows, K, nout))
 
 
-def head_fwd_mse(H, W, bias, target, yhat, dy, loss, scratch_buf, stream=None):
+def head_fwd_mse(H, W, bias, target, yhat, dy, loss, scratch_buf, stream=None, grad_scale: float = 1.0):
+    """H, W: bf16 (bf16 training) or fp32 (fp32 training); everything else fp32."""
     rows, K = H.shape
     nout = W.shape[0]
-    _lib.check(L().b200dp_head_fwd_mse(H.data_ptr(), H.stride(0), W.data_ptr(), bias.data_ptr(), target.data_ptr(),
-                                       rows, K, nout, yhat.data_ptr(), dy.data_ptr(), loss.data_ptr(),
-                                       scratch_buf.data_ptr(), scratch_buf.numel(), _lib.stream_ptr(stream)))
+    assert H.dtype == W.dtype and H.dtype in (torch.bfloat16, torch.float32)
+    _lib.check(L().b200dp_head_fwd_mse(H.data_ptr(), H.stride(0), W.data_ptr(), int(H.dtype == torch.float32),
+                                       bias.data_ptr(), target.data_ptr(), rows, K, nout, yhat.data_ptr(),
+                                       dy.data_ptr(), loss.data_ptr(), grad_scale, scratch_buf.data_ptr(),
+                                       scratch_buf.numel(), _lib.stream_ptr(stream)))
     _lib.count()
 
 
-def head_bwd(dy, W, H, dH: Optional[torch.Tensor], dW, db, scratch_buf, stream=None):
+def head_bwd(dy, W, H, dH: Optional[torch.Tensor], dW, db, scratch_buf, stream=None,
+             db_prev: Optional[torch.Tensor] = None):
+    """``db_prev`` (needs ``dH``): receives the column sums of dH = the bias gradient of the layer
+    below, fused into the same pass."""
     rows, K = H.shape
     nout = W.shape[0]
-    assert dW.dtype == db.dtype
-    _lib.check(L().b200dp_head_bwd(dy.data_ptr(), W.data_ptr(), H.data_ptr(), H.stride(0), rows, K, nout,
+    assert dW.dtype == db.dtype and H.dtype == W.dtype and (dH is None or dH.dtype == H.dtype)
+    assert db_prev is None or (dH is not None and db_prev.dtype == dW.dtype and db_prev.numel() >= K)
+    _lib.check(L().b200dp_head_bwd(dy.data_ptr(), W.data_ptr(), H.data_ptr(), H.stride(0),
+                                   int(H.dtype == torch.float32), rows, K, nout,
                                    _lib.ptr(dH), dH.stride(0) if dH is not None else 0, dW.data_ptr(),
-                                   db.data_ptr(), int(dW.dtype == torch.bfloat16), scratch_buf.data_ptr(),
-                                   scratch_buf.numel(), _lib.stream_ptr(stream)))
+                                   db.data_ptr(), _lib.ptr(db_prev), int(dW.dtype == torch.bfloat16),
+                                   scratch_buf.data_ptr(), scratch_buf.numel(), _lib.stream_ptr(stream)))
     _lib.count(2)
 
 
@@ -131,9 +141,9 @@ def colsum_scratch_bytes(rows: int, n: int) -> int:
 
 def colsum(A, out, scratch_buf, stream=None):
     rows, n = A.shape
-    _lib.check(L().b200dp_colsum_bf16(A.data_ptr(), A.stride(0), rows, n, out.data_ptr(),
-                                      int(out.dtype == torch.bfloat16), scratch_buf.data_ptr(),
-                                      scratch_buf.numel(), _lib.stream_ptr(stream)))
+    _lib.check(L().b200dp_colsum(A.data_ptr(), int(A.dtype == torch.float32), A.stride(0), rows, n, out.data_ptr(),
+                                 int(out.dtype == torch.bfloat16), scratch_buf.data_ptr(),
+                                 scratch_buf.numel(), _lib.stream_ptr(stream)))
     _lib.count(2)
 
 

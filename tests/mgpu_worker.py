@@ -84,6 +84,58 @@ def main():
         out["rows"] = t.shard.rows
         out["fingerprint"] = t.flat.fingerprint()
         t.close()
+    elif scenario.startswith("oracle_"):
+        # >= 1 MB of gradients (so auto would pick two-shot / NVLS), UNEVEN rows + sample weighting, 20
+        # steps: bit-equal replicas (shadow AND fp32 biases) and parameters within 1e-3 of a single-
+        # process fp32 model of ref.py:188-211.  lr 0.01: at 0.05 the fp32 model itself diverges here.
+        import hashlib
+        from b200dp.data import make_randn_rows
+        from b200dp.models.mlp import MLP
+        sync = scenario[7:]
+        sizes, steps, lr, mu = [512, 2048, 512, 1], 20, 0.01, 0.9
+        rows_total = 128 * comm.size + comm.size - 1
+        cfg = TrainConfig(quiet=True, sync=sync, nepochs=steps, n_samples=rows_total, n_features=sizes[0],
+                          hidden=sizes[1:-1], dtype="bf16", data_source="randn", data_dist="local", scale="none",
+                          lr=lr, momentum=mu, noise=0.1, init="torch_cpu", grad_weighting="samples",
+                          check_replicas_every=5)
+        t = Trainer(cfg, comm, dev)
+        out["losses"] = [h["loss"] for h in t.train()]
+        out["sync"] = t._runtime.sync_name
+        out["rows"] = t.shard.rows
+        out["fingerprint"] = t.flat.fingerprint()
+        hb = hashlib.blake2b(digest_size=8)
+        for l in range(t.spec.num_layers):
+            hb.update(t.flat.bias(l).detach().cpu().numpy().tobytes())
+        out["bias_hash"] = hb.hexdigest()
+        sd = t.state_dict()                       # collective: gathers the sharded fp32 master
+        if comm.rank == 0:
+            counts = list(t.counts)
+            torch.manual_seed(cfg.seed)
+            m = MLP(sizes).to(dev)
+            m0 = {k: v.clone() for k, v in m.state_dict().items()}
+            opt = torch.optim.SGD(m.parameters(), lr=lr, momentum=mu)
+            params = list(m.parameters())
+            shards, lo = [], 0
+            for c in counts:
+                d = make_randn_rows(lo, lo + c, sizes[0], 0.1, cfg.data_seed, 1)
+                shards.append((torch.from_numpy(d[:, :sizes[0]]).float().to(dev),
+                               torch.from_numpy(d[:, sizes[0]:]).float().to(dev)))
+                lo += c
+            for _ in range(steps):
+                per_rank = []
+                for x, y in shards:
+                    opt.zero_grad()
+                    torch.nn.functional.mse_loss(m(x), y).backward()
+                    per_rank.append([p.grad.clone() for p in params])
+                for k, p in enumerate(params):
+                    acc = torch.zeros_like(p)
+                    for r, g in enumerate(per_rank):
+                        acc = acc + float(counts[r]) * g[k]
+                    p.grad = acc / float(sum(counts))
+                opt.step()
+            out["err"] = {k: float((sd[k].to(dev) - v).abs().max()) for k, v in m.state_dict().items()}
+            out["moved"] = {k: float((v - m0[k]).abs().max()) for k, v in m.state_dict().items()}
+        t.close()
     sys.stdout.write("\nRESULT " + json.dumps(out) + "\n")     # one write: ranks share the pipe
     sys.stdout.flush()
     import torch.distributed as dist

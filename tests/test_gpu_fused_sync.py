@@ -97,6 +97,74 @@ def test_watchdog_flags_a_peer_that_never_arrives():
     a = ar.make_args(0, 2, [b.data_ptr() for b in bufs], [b.data_ptr() for b in bufs], None,
                      [f.data_ptr() for f in flags], mom.data_ptr(), epochs.data_ptr(), err.data_ptr(),
                      [1.0, 1.0], 2.0, False, 0, True, 1, timeout_ms=50)
+    bufs[0].fill_(1.0)                   # "gradients" that must NOT be applied
     ar.launch(a, 0, n, 0.1, 0.9, False)
     torch.cuda.synchronize()
     assert int(err.item()) == 2          # 1 + index of the missing peer
+    # a timed-out launch changes nothing: no update from stale peer memory, no momentum, no epoch bump
+    assert float(bufs[0].min()) == 1.0 and float(bufs[0].max()) == 1.0
+    assert float(mom.abs().max()) == 0.0 and int(epochs.abs().max()) == 0
+
+
+@pytest.mark.parametrize("world", [2, 3, 8])
+def test_replicated_tail_keeps_fp32_biases_identical_on_every_rank(world):
+    """bf16 two-shot keeps the fp32 master of a slice on its owner only - except the tail of the
+    bucket (a layer's biases), which kernels read in fp32 on every rank: with replicate_tail the
+    owner writes those fp32 values into all peers (round-1 bug: non-owners kept their initial bias)."""
+    from b200dp.ops import allreduce_sgd as ar
+    dev, n, tail, steps, lr, mu = "cuda", 128 * 24, 128 * 3, 4, 0.05, 0.9
+    torch.manual_seed(11)
+    p0 = torch.randn(n, device=dev)
+    params = [p0.clone() for _ in range(world)]
+    shadow = [p0.bfloat16() for _ in range(world)]
+    grads = [torch.zeros(n, device=dev, dtype=torch.bfloat16) for _ in range(world)]
+    flags = [torch.zeros(ar.SYNC_MAX_BLOCKS * 8, device=dev, dtype=torch.int32) for _ in range(world)]
+    mom = [torch.zeros(n, device=dev) for _ in range(world)]
+    epochs = [torch.zeros(ar.SYNC_MAX_BLOCKS, device=dev, dtype=torch.int32) for _ in range(world)]
+    err = [torch.zeros(1, device=dev, dtype=torch.int32) for _ in range(world)]
+    args = [ar.make_args(r, world, [g.data_ptr() for g in grads], [p.data_ptr() for p in params],
+                         [s_.data_ptr() for s_ in shadow], [f.data_ptr() for f in flags], mom[r].data_ptr(),
+                         epochs[r].data_ptr(), err[r].data_ptr(), [1.0] * world, float(world), True, 1, False, 0, 5000)
+            for r in range(world)]
+    dargs = torch.zeros(ar.device_args_bytes() * world, device=dev, dtype=torch.uint8)
+    ref_p = torch.nn.Parameter(p0.clone())
+    opt = torch.optim.SGD([ref_p], lr=lr, momentum=mu)
+    for s_ in range(steps):
+        gs = [torch.randn(n, device=dev).bfloat16() for _ in range(world)]
+        for r in range(world):
+            grads[r].copy_(gs[r])
+        ar.launch_emulated(args, 0, n, lr, mu, False, dargs, replicate_tail=tail)
+        acc = torch.zeros(n, device=dev)
+        for r in range(world):
+            acc = acc + gs[r].float()
+        ref_p.grad = acc / world
+        opt.step()
+    torch.cuda.synchronize()
+    assert all(int(e.item()) == 0 for e in err)
+    for r in range(world):
+        torch.testing.assert_close(params[r][n - tail:], ref_p.detach()[n - tail:], rtol=2e-5, atol=2e-6)
+        assert torch.equal(params[r][n - tail:], params[0][n - tail:])       # bit-equal fp32 tail everywhere
+        assert torch.equal(shadow[r], shadow[0])
+    # outside the tail a non-owner's master is untouched (still the initial value): sharded on purpose
+    vn, units = 8, n // 8
+    lo0, hi0 = 0, units // world * vn
+    assert torch.equal(params[world - 1][lo0:hi0], p0[lo0:hi0])
+
+
+def test_nvls_mode_refuses_unequal_weights():
+    """The NVSwitch sums its inputs as they are; per-rank weights must be folded into the gradients
+    by the caller (round-1 bug: they were silently ignored)."""
+    from b200dp.ops import allreduce_sgd as ar
+    from b200dp.ops._lib import B200dpError
+    dev, n = "cuda", 1024
+    bufs = [torch.zeros(n, device=dev) for _ in range(2)]
+    flags = [torch.zeros(ar.SYNC_MAX_BLOCKS * 8, device=dev, dtype=torch.int32) for _ in range(2)]
+    mom = torch.zeros(n, device=dev)
+    epochs = torch.zeros(ar.SYNC_MAX_BLOCKS, device=dev, dtype=torch.int32)
+    err = torch.zeros(1, device=dev, dtype=torch.int32)
+    a = ar.make_args(0, 2, [b.data_ptr() for b in bufs], [b.data_ptr() for b in bufs], None,
+                     [f.data_ptr() for f in flags], mom.data_ptr(), epochs.data_ptr(), err.data_ptr(),
+                     [9.0, 8.0], 17.0, False, 2, True, 1, timeout_ms=50,
+                     mc_grads=bufs[0].data_ptr(), mc_params=bufs[0].data_ptr())
+    with pytest.raises(B200dpError, match="equal per-rank weights"):
+        ar.launch(a, 0, n, 0.1, 0.9, False)

@@ -54,11 +54,14 @@ def test_mse_loss_grad(n, pred_dtype, dy_dtype):
 
 
 @pytest.mark.parametrize("rows,K_,nout", [(64, 256, 1), (1000, 4096, 1), (333, 512, 3), (8192, 4096, 1)])
-def test_head_fwd_bwd(rows, K_, nout):
+@pytest.mark.parametrize("edt", [torch.bfloat16, torch.float32])
+def test_head_fwd_bwd(rows, K_, nout, edt):
+    """GEMV head + MSE + dY, and its backward with the fused column sums of dH (= the bias gradient
+    of the layer below); bf16 elements (bf16 training) and fp32 elements (fp32 training)."""
     from b200dp.ops import kernels as K
     torch.manual_seed(3)
-    H = torch.relu(torch.randn(rows, K_, device="cuda")).bfloat16()
-    W = (torch.randn(nout, K_, device="cuda") / K_ ** 0.5).bfloat16()
+    H = torch.relu(torch.randn(rows, K_, device="cuda")).to(edt)
+    W = (torch.randn(nout, K_, device="cuda") / K_ ** 0.5).to(edt)
     b = torch.randn(nout, device="cuda")
     y = torch.randn(rows, nout, device="cuda")
     yhat = torch.empty(rows, nout, device="cuda")
@@ -70,24 +73,51 @@ def test_head_fwd_bwd(rows, K_, nout):
     torch.testing.assert_close(yhat, ref, rtol=1e-4, atol=1e-4)
     torch.testing.assert_close(loss, ((ref - y) ** 2).mean(), rtol=1e-4, atol=1e-6)
     torch.testing.assert_close(dy, 2 * (ref - y) / (rows * nout), rtol=1e-3, atol=1e-7)
-    for gdt in (torch.float32, torch.bfloat16):
-        dH = torch.empty(rows, K_, device="cuda", dtype=torch.bfloat16)
+    # a rank's all-reduce weight folded into the loss gradient (the loss itself is not scaled)
+    dy3, loss3 = torch.empty_like(dy), torch.zeros((), device="cuda")
+    K.head_fwd_mse(H, W, b, y, yhat, dy3, loss3, scratch, grad_scale=3.0)
+    torch.testing.assert_close(dy3, 3.0 * dy, rtol=1e-6, atol=0)
+    assert torch.equal(loss3, loss)
+    grad_dtypes = (torch.float32, torch.bfloat16) if edt == torch.bfloat16 else (torch.float32,)
+    for gdt in grad_dtypes:
+        dH = torch.empty(rows, K_, device="cuda", dtype=edt)
         dW = torch.empty(nout, K_, device="cuda", dtype=gdt)
         db = torch.empty(nout, device="cuda", dtype=gdt)
-        K.head_bwd(dy, W, H, dH, dW, db, scratch)
+        dbp = torch.full((K_,), float("nan"), device="cuda", dtype=gdt)
+        K.head_bwd(dy, W, H, dH, dW, db, scratch, db_prev=dbp)
         tol = dict(rtol=2e-2, atol=1e-5) if gdt == torch.bfloat16 else dict(rtol=1e-3, atol=1e-6)
         torch.testing.assert_close(dW.float(), dy.t() @ H.float(), **tol)
         torch.testing.assert_close(db.float(), dy.sum(0), **tol)
-        torch.testing.assert_close(dH.float(), (dy @ W.float()) * (H.float() > 0), rtol=1e-2, atol=1e-7)
+        want_dh = (dy @ W.float()) * (H.float() > 0)
+        torch.testing.assert_close(dH.float(), want_dh, rtol=1e-2 if edt == torch.bfloat16 else 1e-4, atol=1e-7)
+        torch.testing.assert_close(dbp.float(), want_dh.sum(0), **tol)
+        # without db_prev nothing else changes
+        dW2, db2 = torch.empty_like(dW), torch.empty_like(db)
+        K.head_bwd(dy, W, H, dH, dW2, db2, scratch)
+        assert torch.equal(dW2, dW) and torch.equal(db2, db)
 
 
 @pytest.mark.parametrize("rows,n", [(64, 8), (1000, 4096), (8192, 1024)])
-def test_colsum(rows, n):
+@pytest.mark.parametrize("edt", [torch.bfloat16, torch.float32])
+def test_colsum(rows, n, edt):
     from b200dp.ops import kernels as K
-    A = torch.randn(rows, n, device="cuda").bfloat16()
+    A = torch.randn(rows, n, device="cuda").to(edt)
     out = torch.empty(n, device="cuda")
     K.colsum(A, out, K.scratch(K.colsum_scratch_bytes(rows, n), "cuda"))
     torch.testing.assert_close(out, A.float().sum(0), rtol=1e-4, atol=1e-3)
+
+
+def test_mse_grad_scale_and_denominator():
+    from b200dp.ops import kernels as K
+    torch.manual_seed(5)
+    n = 4096
+    pred, tgt = torch.randn(n, device="cuda"), torch.randn(n, device="cuda")
+    dy, loss = torch.empty(n, device="cuda"), torch.zeros((), device="cuda")
+    scratch = K.scratch(K.mse_scratch_bytes(n), "cuda")
+    K.mse_loss_grad(pred, tgt, dy, loss, scratch, grad_scale=5.0, denom=n // 2)
+    d = pred - tgt
+    torch.testing.assert_close(loss, (d * d).sum() / (n // 2), rtol=1e-5, atol=1e-7)
+    torch.testing.assert_close(dy, 5.0 * 2 * d / (n // 2), rtol=1e-6, atol=1e-9)
 
 
 @pytest.mark.parametrize("gdt", [torch.float32, torch.bfloat16])

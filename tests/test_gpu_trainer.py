@@ -186,3 +186,99 @@ def test_row_chunked_wgrad_and_buckets_are_bitwise_neutral():
     la = [h["loss"] for h in a.train()]
     lb = [h["loss"] for h in b.train()]
     assert la == lb and a.flat.fingerprint() == b.flat.fingerprint()
+
+
+def _autograd_reference(t, round_bf16):
+    m = t.flat.as_module().cuda()
+    if round_bf16:
+        for p in m.parameters():
+            p.data = p.data.bfloat16().float()
+    x32, y32 = t.shard.x.cuda(), t.shard.y.cuda()
+    if round_bf16:
+        x32 = x32.bfloat16().float()
+    loss = torch.nn.functional.mse_loss(m(x32), y32)
+    loss.backward()
+    return m, loss.detach()
+
+
+def test_fp32_model_beyond_the_simt_kernel_runs_on_tf32_tensor_cores():
+    """`--dtype fp32` (the reference's only precision, ref.py:159) for a model far beyond the SIMT
+    kernel's 64-wide limit: kind::tf32 GEMMs on the fp32 parameters, fp32 gradients and update."""
+    from b200dp.config import TrainConfig
+    from b200dp.engine import Trainer
+    cfg = TrainConfig(quiet=True, nepochs=0, hidden=[512, 200], n_features=96, n_samples=1024, dtype="fp32",
+                      data_source="randn", data_dist="local", scale="none", lr=0.01, noise=0.1)
+    t = Trainer(cfg, device=torch.device("cuda"))
+    assert t.compute.name == "cuda-tcgen05" and t.flat.shadow is None and t.flat.grads.dtype == torch.float32
+    m, ref_loss = _autograd_reference(t, round_bf16=False)
+    loss = t.compute.loss_and_grads(t.x, t.y)
+    torch.testing.assert_close(loss, ref_loss, rtol=5e-3, atol=1e-4)
+    for seg, p in zip(t.spec.segments, m.parameters()):
+        got = t.flat._logical(t.flat.grads, seg)
+        scale = p.grad.abs().max().item() + 1e-12
+        assert (got - p.grad).abs().max().item() <= 1e-2 * scale, seg.key      # TF32 operands: ~1e-3 relative
+    first = float(loss.item())
+    for _ in range(30):
+        last = t.step(t.x, t.y)
+    assert float(last.item()) < 0.9 * first
+    # evaluation runs on the same kernels
+    pred = t.predict(t.shard.x[:64])
+    want = t.flat.as_module().cuda()(t.shard.x[:64].cuda())
+    torch.testing.assert_close(pred, want, rtol=1e-2, atol=1e-2)
+    t.close()
+
+
+@pytest.mark.parametrize("nout", [5, 12])
+def test_heads_with_5_to_15_outputs_are_padded_to_the_gemm_head(nout):
+    from b200dp.config import TrainConfig
+    from b200dp.engine import Trainer
+    cfg = TrainConfig(quiet=True, nepochs=0, hidden=[256, 128], n_features=64, n_samples=1024, n_outputs=nout,
+                      dtype="bf16", data_source="randn", data_dist="local", scale="none", lr=0.01, noise=0.1)
+    t = Trainer(cfg, device=torch.device("cuda"))
+    assert t.spec.sizes[-1] == (nout + 7) // 8 * 8 and t.spec.logical_sizes[-1] == nout
+    m, ref_loss = _autograd_reference(t, round_bf16=True)
+    loss = t.compute.loss_and_grads(t.x, t.y)
+    torch.testing.assert_close(loss, ref_loss, rtol=2e-2, atol=1e-3)
+    for seg, p in zip(t.spec.segments, m.parameters()):
+        got = t.flat._logical(t.flat.grads, seg).float()
+        scale = p.grad.abs().max().item() + 1e-12
+        assert (got - p.grad).abs().max().item() <= 5e-2 * scale, seg.key
+        full = t.flat._view(t.flat.grads, seg).float()                   # padding rows receive exactly zero
+        assert float(full.abs().sum()) == pytest.approx(float(got.abs().sum()), rel=1e-6)
+    assert tuple(t.state_dict()[f"layers.{2 * (t.spec.num_layers - 1)}.weight"].shape) == (nout, 128)
+    assert t.predict(t.shard.x[:8]).shape == (8, nout)
+    t.close()
+
+
+def test_headline_shape_three_steps_against_bf16_autograd():
+    """The benchmark's own configuration (12288 -> 4 x 4096 -> 1, 8192 rows, wgrad of layer 0 in row
+    chunks, CTA-pair GEMMs with fused column sums, half-tile tail waves) for three steps: before every
+    step the loss and all gradients are compared with an autograd model built from the trainer's
+    current parameters (weights rounded to bf16, fp32 biases)."""
+    from b200dp.config import TrainConfig
+    from b200dp.engine import Trainer
+    cfg = TrainConfig(quiet=True, nepochs=0, n_samples=8192, n_features=12288, hidden=[4096] * 4, dtype="bf16",
+                      data_source="randn", data_dist="local", scale="none", init="device", lr=1e-4, noise=0.1)
+    t = Trainer(cfg, device=torch.device("cuda"))
+    assert len(t._runtime.sync.chunks_of[0]) > 1                          # chunked wgrad of the 12288-wide layer
+    x32, y32 = t.x.float(), t.y
+    losses = []
+    for step in range(3):
+        m = t.flat.as_module().cuda()
+        with torch.no_grad():
+            for p in m.parameters():
+                if p.dim() == 2:
+                    p.copy_(p.bfloat16().float())
+        ref_loss = torch.nn.functional.mse_loss(m(x32), y32)
+        ref_loss.backward()
+        loss = t.compute.loss_and_grads(t.x, t.y)                          # gradients only (no update queued)
+        torch.cuda.synchronize()
+        assert float(loss.item()) == pytest.approx(float(ref_loss.item()), rel=2e-2), step
+        for seg, p in zip(t.spec.segments, m.parameters()):
+            got = t.flat._logical(t.flat.grads, seg).float()
+            scale = p.grad.abs().max().item() + 1e-12
+            assert (got - p.grad).abs().max().item() <= 5e-2 * scale, (step, seg.key)
+        del m, ref_loss
+        losses.append(float(t.step(t.x, t.y).item()))                      # the real step: same gradients + update
+    assert losses[2] < losses[0]
+    t.close()

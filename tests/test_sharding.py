@@ -60,3 +60,31 @@ def test_shard_properties(rows, world):
     ws = grad_weights(rows, world, "samples") if rows else None
     if ws:
         assert abs(sum(ws) - 1.0) < 1e-9
+
+
+def test_spread_placement_takes_one_gpu_per_pcie_switch_first():
+    """launch.spread_devices: a 2- or 4-rank run on an 8-GPU HGX board (GPU pairs share a PCIe switch and
+    its x16 uplink) must not put two ranks on one switch while another switch is idle."""
+    from b200dp.launch import spread_devices
+    c = [[0] * 8 for _ in range(8)]
+    for i in range(8):
+        for j in range(8):
+            if i != j:
+                c[i][j] = 40 if i // 2 == j // 2 else (20 if i // 4 == j // 4 else 10)
+    assert spread_devices(2, c, 8) == [0, 4]
+    assert sorted(d // 2 for d in spread_devices(4, c, 8)) == [0, 1, 2, 3]
+    assert spread_devices(8, c, 8) == list(range(8))
+    assert spread_devices(3, None, 8) == [0, 1, 2]                   # no topology data: identity
+
+
+def test_bench_counts_executed_flops():
+    import importlib.util
+    import os
+    spec = importlib.util.spec_from_file_location("bench", os.path.join(os.path.dirname(__file__), "..", "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    sizes, rows = [12288, 4096, 4096, 4096, 4096, 1], 8192
+    full = sum(sizes[i] * sizes[i + 1] for i in range(5))
+    # forward + wgrad for every layer, dgrad for all but the first: 4.12 TFLOP, not the 4.95 of 6*N*D
+    assert bench.executed_flops(sizes, rows) == 2.0 * rows * (3 * full - sizes[0] * sizes[1])
+    assert abs(bench.executed_flops(sizes, rows) / 1e12 - 4.124) < 0.01
