@@ -173,8 +173,9 @@ def bare_h2d_ms(nbytes_x, nbytes_y, world, iters=6):
     """All ranks copy one step's input bytes from pinned host memory at the same time, nothing else
     running: the PCIe floor of the end-to-end step on this box at this N (max over ranks)."""
     import torch
-    hx = torch.empty(nbytes_x, dtype=torch.uint8).pin_memory()
-    hy = torch.empty(max(nbytes_y, 1), dtype=torch.uint8).pin_memory()
+    from b200dp.data import PinnedBuffer
+    bx, by = PinnedBuffer((nbytes_x,), torch.uint8), PinnedBuffer((max(nbytes_y, 1),), torch.uint8)
+    hx, hy = bx.tensor, by.tensor
     dx = torch.empty(nbytes_x, dtype=torch.uint8, device="cuda")
     dy = torch.empty(max(nbytes_y, 1), dtype=torch.uint8, device="cuda")
     for _ in range(2):
@@ -188,7 +189,10 @@ def bare_h2d_ms(nbytes_x, nbytes_y, world, iters=6):
     e1.record()
     torch.cuda.synchronize()
     barrier(world)
-    return max_over_ranks(e0.elapsed_time(e1) / iters, world)
+    ms = e0.elapsed_time(e1) / iters
+    del hx, hy
+    bx.close(); by.close()
+    return max_over_ranks(ms, world)
 
 
 # ------------------------------------------------------------------------------------------- ours
@@ -268,8 +272,12 @@ def measure_ours(args, config_name, rank, world, sampler, extras=True):
     # ---- end to end: pinned host batches, H2D every step, loss read back every step -----------
     e2e = None
     if not args.no_e2e:
-        xh = [t.shard.x.to(t.x.dtype).pin_memory(), t.shard.x.to(t.x.dtype).clone().pin_memory()]
-        yh = [t.shard.y.pin_memory(), t.shard.y.clone().pin_memory()]
+        # host batches in the framework's pinned staging buffers (data.PinnedBuffer: huge-page advised,
+        # cudaHostRegister'ed) - what a user of the host-fed API is told to allocate
+        from b200dp.data import pinned_like
+        hb = [pinned_like(t.shard.x.to(t.x.dtype)), pinned_like(t.shard.x.to(t.x.dtype)),
+              pinned_like(t.shard.y), pinned_like(t.shard.y)]
+        xh, yh = [hb[0].tensor, hb[1].tensor], [hb[2].tensor, hb[3].tensor]
 
         def batches():
             i = 0
@@ -301,6 +309,8 @@ def measure_ours(args, config_name, rank, world, sampler, extras=True):
             e2e["bound"] = "pcie" if floor > 0.9 * ms_per_step else "compute"
             e2e["fraction_of_bound"] = max(floor, ms_per_step) / ems
         del xh, yh
+        for b in hb:
+            b.close()
 
     spec = t.spec
     rec = {
@@ -333,7 +343,8 @@ def measure_ours(args, config_name, rank, world, sampler, extras=True):
 def run_ours(args, rank, world):
     import torch
     from b200dp.utils.clocks import ClockSampler
-    sampler = ClockSampler(torch.cuda.current_device(), period_ms=20).start() if rank == 0 else None
+    period = int(os.environ.get("B200DP_CLOCK_PERIOD_MS", "20"))
+    sampler = ClockSampler(torch.cuda.current_device(), period_ms=period).start() if (rank == 0 and period > 0) else None
     if sampler is not None:
         sampler.wait_first_sample(2.0)
     rec = measure_ours(args, args.config, rank, world, sampler)
@@ -427,9 +438,10 @@ def measure_torch(args, config_name, rank, world, sampler):
         loss = loss_fn(net(xb).float(), yb)
         loss.backward()                                        # DDP: bucketed all-reduce (mean) under backward
         if mixed:
-            torch._foreach_copy_(master_grads, [p.grad for p in params])
-            opt.step()
-            torch._foreach_copy_(params, master)
+            with torch.no_grad():
+                torch._foreach_copy_(master_grads, [p.grad for p in params])
+                opt.step()
+                torch._foreach_copy_(params, master)
         else:
             opt.step()
         return loss
@@ -449,8 +461,9 @@ def measure_torch(args, config_name, rank, world, sampler):
 
     if not args.no_e2e:
         # host-fed: pinned batches, H2D of step i+1 under step i on a copy stream, loss read back per step
-        xh = [x.cpu().pin_memory(), x.cpu().pin_memory()]
-        yh = [y.cpu().pin_memory(), y.cpu().pin_memory()]
+        from b200dp.data import pinned_like          # the same staging allocator as the other arm
+        hb = [pinned_like(x.cpu()), pinned_like(x.cpu()), pinned_like(y.cpu()), pinned_like(y.cpu())]
+        xh, yh = [hb[0].tensor, hb[1].tensor], [hb[2].tensor, hb[3].tensor]
         slots = [(torch.empty_like(x), torch.empty_like(y)) for _ in range(2)]
         copy_stream = torch.cuda.Stream(device=dev)
         main = torch.cuda.current_stream()
@@ -501,6 +514,9 @@ def measure_torch(args, config_name, rank, world, sampler):
         h2d = x.numel() * x.element_size() + y.numel() * y.element_size()
         rec["e2e"] = {"value": rows_total / (ems * 1e-3), "unit": "samples/s", "ms_per_step": ems,
                       "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4}
+        del xh, yh
+        for b in hb:
+            b.close()
     del net, model, opt, params
     torch.cuda.empty_cache()
     return rec

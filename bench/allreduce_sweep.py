@@ -22,7 +22,40 @@ from b200dp.ops import allreduce_sgd as ar, kernels as K  # noqa: E402
 from b200dp.ops.cuda_backend import SymmLayout  # noqa: E402
 from b200dp.parallel.comm import world_comm  # noqa: E402
 
-LINK_GBS = 770.0
+LINK_GBS = 770.0          # B200_PROFILING.md: measured peer copy per direction; re-measured here (peer_copy rows)
+
+
+class _Raw:
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+
+
+def nvlink_bytes(dev_index):
+    """(tx, rx) payload bytes this GPU has moved over all its NVLinks so far (NVML throughput counters,
+    KiB granularity), or None when the counters are not exposed."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        uuid = torch.cuda.get_device_properties(dev_index).uuid
+        h = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + str(uuid)).encode())
+        tx_id = getattr(pynvml, "NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_TX", 138)
+        rx_id = getattr(pynvml, "NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_RX", 139)
+        try:
+            vals = pynvml.nvmlDeviceGetFieldValues(h, [(tx_id, 0xFFFFFFFF), (rx_id, 0xFFFFFFFF)])   # all links
+            out = [int(v.value.ullVal) for v in vals]
+            if all(v.nvmlReturn == 0 for v in vals):
+                return out[0] * 1024, out[1] * 1024
+        except Exception:
+            pass
+        tx = rx = 0
+        for link in range(18):
+            vals = pynvml.nvmlDeviceGetFieldValues(h, [(tx_id, link), (rx_id, link)])
+            if any(v.nvmlReturn != 0 for v in vals):
+                continue
+            tx += int(vals[0].value.ullVal); rx += int(vals[1].value.ullVal)
+        return tx * 1024, rx * 1024
+    except Exception:
+        return None
 
 
 def timed(fn, iters, world):
@@ -83,9 +116,17 @@ def main():
                              epochs.data_ptr(), err.data_ptr(), w, float(world), bf16, mode, not bf16,
                              args.blocks, 20000, symm.mc("grads"), symm.mc("shadow") if bf16 else None,
                              symm.mc("params"))
+            c0 = nvlink_bytes(dev.index) if nbytes >= (16 << 20) else None
             ms = timed(lambda: ar.launch(a, 0, n, 1e-6, 0.9, False), iters, world)
             rec[name + "_us"] = ms * 1e3
             rec[name + "_busbw_gbs"] = 2 * (world - 1) / world * n * esz / (ms * 1e-3) / 1e9
+            if c0 is not None:
+                torch.cuda.synchronize()
+                c1 = nvlink_bytes(dev.index)
+                if c1 is not None:                      # timed() runs 3 warm-up + iters launches
+                    calls = iters + 3
+                    rec[name + "_nvlink_tx_bytes_per_call"] = (c1[0] - c0[0]) / calls
+                    rec[name + "_nvlink_rx_bytes_per_call"] = (c1[1] - c0[1]) / calls
         # NCCL all-reduce + our local SGD kernel
         g = grads[:n]
         def nccl():
@@ -109,8 +150,19 @@ def main():
                 K.sgd_momentum(params[:n], acc.to(dev), mom[:n], shadow[:n] if bf16 else None, 1e-6, 0.9, False)
             ms = timed(gather_root, 3, world)
             rec["gather_root_us"] = ms * 1e3
-        best = min(v for k, v in rec.items() if k.endswith("_us") and not k.startswith(("nccl", "gather")))
+        # plain peer copy over NVLink (every rank pulls from its right neighbour at the same time): the
+        # link-rate denominator SURVEY 6.2 asks to be measured on this box
+        if nbytes >= (1 << 20):
+            peer = (rank + 1) % world
+            src = torch.as_tensor(_Raw(symm.ptrs("grads")[peer], n * esz), device=dev)
+            dst = torch.empty(n * esz, dtype=torch.uint8, device=dev)
+            ms = timed(lambda: dst.copy_(src, non_blocking=True), iters, world)
+            rec["peer_copy_us"] = ms * 1e3
+            rec["peer_copy_gbs"] = n * esz / (ms * 1e-3) / 1e9
+            del dst
+        best = min(v for k, v in rec.items() if k.endswith("_us") and not k.startswith(("nccl", "gather", "peer")))
         link_bytes = 2 * (world - 1) / world * n * esz
+        rec["algorithmic_link_bytes_twoshot"] = link_bytes
         rec["roofline_us"] = link_bytes / (LINK_GBS * 1e9) * 1e6
         rec["best_frac_of_link_roofline"] = rec["roofline_us"] / best
         rows.append(rec)

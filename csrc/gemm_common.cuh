@@ -46,9 +46,9 @@ struct GemmParams {
   int num_m_blocks, num_n_blocks;
   int group_m;                 // rasterisation: tiles are visited in bands of group_m row-blocks
   // fused column sums of the stored result (db of the layer below = sum over rows of its dY):
-  // every 128-row strip writes its partial sums to cs_partials[strip][cs_ld]; the last strip to
-  // finish a column block (ticket) adds the strips in strip order - a fixed summation order, so the
-  // result is bit-reproducible - and writes cs_out.  Tickets start at zero and are left at zero.
+  // every 128-row strip writes its partial sums to cs_partials[strip][cs_ld]; the last epilogue warp
+  // to finish a column block (ticket) adds the strips in strip order - a fixed summation order, so
+  // the result is bit-reproducible - and writes cs_out.  Tickets start at zero and are left at zero.
   float* cs_partials;
   unsigned int* cs_tickets;
   void* cs_out;
@@ -208,41 +208,74 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, const uint32
   }
 }
 
-// The part of the column-sum fusion that runs once per tile, after the TMEM stage was released:
-// combine the four quadrants (fixed order), publish this strip's partial row, and let the last
-// strip of the column block do the final fixed-order sum.
+// The part of the column-sum fusion that runs once per tile, after the TMEM stage was released.  One
+// CTA barrier (all four quadrants are in shared memory), then every epilogue warp works alone: it adds
+// the four quadrants of ITS quarter of the columns (fixed order), publishes that piece of the strip's
+// partial row, and takes a ticket (release: fence + atomic by one lane).  The warp that draws the last
+// ticket of a column block (4 per 128-row strip) adds the strips in strip order - a fixed summation
+// order, so the result is bit-reproducible - and writes the bias gradient.  No warp waits for another
+// warp's fence or atomic; the shared buffer is double-buffered by tile parity, so the barrier of the
+// next tile is the only thing that orders its reuse.
 template <int BN>
-__device__ __forceinline__ void colsum_finish(const GemmParams& p, float* cs_smem /* [4][BN] */, int* cs_last,
-                                              int strip, bool strip_ok, int n_blk, int n0, int et /* 0..127 */) {
-  epi_bar_sync();                                  // all four quadrants are in shared memory
-  if (strip_ok) {
-    for (int j = et; j < BN; j += kEpiThreads) {
-      const float s = ((cs_smem[j] + cs_smem[BN + j]) + cs_smem[2 * BN + j]) + cs_smem[3 * BN + j];
-      __stcg(p.cs_partials + (long long)strip * p.cs_ld + n0 + j, s);
-    }
-    __threadfence();
-  }
-  epi_bar_sync();                                  // partial row complete (and cs_smem free again)
-  if (et == 0) {
-    int last = 0;
-    if (strip_ok) last = atomicAdd(p.cs_tickets + n_blk, 1u) == unsigned(p.cs_strips - 1);
-    *cs_last = last;
-  }
+__device__ __forceinline__ void colsum_finish(const GemmParams& p, const float* cs_buf /* [4][BN] */, int strip,
+                                              bool strip_ok, int n_blk, int n0, int quad, int lane) {
   epi_bar_sync();
-  if (*cs_last) {
-    __threadfence();
-    for (int j = et; j < BN; j += kEpiThreads) {
-      const int col = n0 + j;
-      if (col < p.N) {
-        float s = 0.0f;
-#pragma unroll 4
-        for (int st = 0; st < p.cs_strips; ++st) s += __ldcg(p.cs_partials + (long long)st * p.cs_ld + col);
-        if (p.cs_out_bf16) reinterpret_cast<__nv_bfloat16*>(p.cs_out)[col] = __float2bfloat16_rn(s);
-        else reinterpret_cast<float*>(p.cs_out)[col] = s;
+  constexpr int CPW = BN / 4;                      // columns per warp
+  if (strip_ok) {
+#pragma unroll
+    for (int j = lane; j < CPW; j += 32) {
+      const int c = quad * CPW + j;
+      const float s = ((cs_buf[c] + cs_buf[BN + c]) + cs_buf[2 * BN + c]) + cs_buf[3 * BN + c];
+      __stcg(p.cs_partials + (long long)strip * p.cs_ld + n0 + c, s);
+    }
+  }
+  __syncwarp();
+  int last = 0;
+  if (lane == 0 && strip_ok) {
+    __threadfence();                               // cumulative: covers the warp's stores ordered by __syncwarp
+    last = atomicAdd(p.cs_tickets + n_blk, 1u) == unsigned(4 * p.cs_strips - 1);
+  }
+  last = __shfl_sync(0xffffffffu, last, 0);
+  if (!last) return;
+  __threadfence();
+  constexpr int V = BN / 128;                      // float4 vectors per lane: lane owns 4*V consecutive columns
+  float4 acc[V];
+#pragma unroll
+  for (int v = 0; v < V; ++v) acc[v] = make_float4(0.f, 0.f, 0.f, 0.f);
+  const float* base = p.cs_partials + n0 + lane * 4 * V;
+  constexpr int U = 8;                             // strips in flight per round
+  for (int st = 0; st < p.cs_strips; st += U) {
+    float4 t[U][V];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+#pragma unroll
+      for (int v = 0; v < V; ++v) {
+        t[u][v] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (st + u < p.cs_strips)
+          t[u][v] = __ldcg(reinterpret_cast<const float4*>(base + (long long)(st + u) * p.cs_ld) + v);
       }
     }
-    if (et == 0) p.cs_tickets[n_blk] = 0;          // reusable by the next launch on the stream
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+#pragma unroll
+      for (int v = 0; v < V; ++v) {
+        acc[v].x += t[u][v].x; acc[v].y += t[u][v].y; acc[v].z += t[u][v].z; acc[v].w += t[u][v].w;
+      }
+    }
   }
+#pragma unroll
+  for (int v = 0; v < V; ++v) {
+    const int col = n0 + lane * 4 * V + v * 4;
+    const float o[4] = {acc[v].x, acc[v].y, acc[v].z, acc[v].w};
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      if (col + e < p.N) {
+        if (p.cs_out_bf16) reinterpret_cast<__nv_bfloat16*>(p.cs_out)[col + e] = __float2bfloat16_rn(o[e]);
+        else reinterpret_cast<float*>(p.cs_out)[col + e] = o[e];
+      }
+    }
+  }
+  if (lane == 0) p.cs_tickets[n_blk] = 0;          // reusable by the next launch on the stream
 }
 
 // One (128-row strip x BN columns) tile of one CTA.  `taddr`: TMEM address of this warp's lane
@@ -250,12 +283,13 @@ __device__ __forceinline__ void colsum_finish(const GemmParams& p, float* cs_sme
 // completed (the MMA warp may then overwrite the stage).
 template <typename T, int BN, typename Release>
 __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t taddr, int m0, int n0, int n_blk,
-                                              int strip, int quad, int lane, float* cs_smem, int* cs_last,
+                                              int strip, int quad, int lane, float* cs_smem, int parity,
                                               Release release) {
   const int row = m0 + quad * 32 + lane;
   const bool row_ok = row < p.M;
   const bool cs = p.cs_out != nullptr;
-  float* cs_row = cs ? cs_smem + quad * BN : nullptr;
+  float* cs_buf = cs_smem + parity * (4 * BN);     // [4][BN] of this tile (double-buffered by tile parity)
+  float* cs_row = cs ? cs_buf + quad * BN : nullptr;
   constexpr int NC = BN / 32;
   static_assert(NC % 2 == 0, "the epilogue ping-pongs two register sets");
   uint32_t va[32], vb[32];
@@ -272,7 +306,7 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t tadd
   tc_fence_before();
   __syncwarp();
   release();
-  if (cs) colsum_finish<BN>(p, cs_smem, cs_last, strip, m0 < p.M, n_blk, n0, quad * 32 + lane);
+  if (cs) colsum_finish<BN>(p, cs_buf, strip, m0 < p.M, n_blk, n0, quad, lane);
 }
 
 // ---- host side ---------------------------------------------------------------------------------

@@ -14,6 +14,8 @@
 // expressed in the UMMA shared-memory descriptor (instruction-descriptor bits 15/16) and the TMA
 // box shape.  The fp32 instantiation reads the reference's own precision (ref.py:159 `.float()`)
 // straight from fp32 buffers; the tensor core rounds the operands to TF32 and accumulates in fp32.
+// It exists for K-major operands only: measured on B200, a kind::tf32 MMA with a transposed operand
+// leaves the accumulator untouched, so the fp32 backward runs on transposed copies instead.
 //
 // Warp roles (192 threads): warp 0 = TMA producer (one lane), warp 1 = TMEM allocator + MMA issuer
 // (one lane), warps 2..5 = epilogue (gemm_common.cuh).  Two TMEM accumulator stages let the
@@ -36,7 +38,7 @@ struct Smem {
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kBarrierOffset = kStages * kStageBytes;
   static constexpr int kColsumOffset = kBarrierOffset + 256;
-  static constexpr int kTotal = kColsumOffset + 4 * BN * 4 + 1024;   // + alignment slack
+  static constexpr int kTotal = kColsumOffset + 2 * 4 * BN * 4 + 1024;   // + alignment slack
 };
 
 template <typename T, int BN, bool A_MN, bool B_MN>
@@ -53,7 +55,6 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   uint64_t* tmem_full = empty_bar + kStages;
   uint64_t* tmem_empty = tmem_full + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
-  int* cs_last = reinterpret_cast<int*>(tmem_slot + 1);
   float* cs_smem = reinterpret_cast<float*>(smem + S::kColsumOffset);
 
   const int warp = threadIdx.x >> 5;
@@ -165,7 +166,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       tc_fence_after();
       const uint32_t taddr = tmem_base + (uint32_t(quad * 32) << 16) + uint32_t(as * BN);
       uint64_t* release_bar = &tmem_empty[as];
-      epilogue_tile<T, BN>(p, taddr, m_blk * BM, n_blk * BN, n_blk, m_blk, quad, lane, cs_smem, cs_last,
+      epilogue_tile<T, BN>(p, taddr, m_blk * BM, n_blk * BN, n_blk, m_blk, quad, lane, cs_smem, it & 1,
                            [&]() { if (lane == 0) mbar_arrive(release_bar); });
     }
   }
@@ -218,9 +219,12 @@ int launch(const b200dp_gemm_args* a, cudaStream_t stream) {
 template <typename T, int BN>
 int dispatch_major(const b200dp_gemm_args* a, cudaStream_t s) {
   if (!a->a_mn_major && !a->b_mn_major) return launch<T, BN, false, false>(a, s);
-  if (!a->a_mn_major && a->b_mn_major) return launch<T, BN, false, true>(a, s);
-  if (a->a_mn_major && a->b_mn_major) return launch<T, BN, true, true>(a, s);
-  return launch<T, BN, true, false>(a, s);
+  if constexpr (!Elem<T>::kTf32) {
+    if (!a->a_mn_major && a->b_mn_major) return launch<T, BN, false, true>(a, s);
+    if (a->a_mn_major && a->b_mn_major) return launch<T, BN, true, true>(a, s);
+    return launch<T, BN, true, false>(a, s);
+  }
+  return fail("gemm_tf32: operands must be K-major");
 }
 
 int validate(const b200dp_gemm_args* a, int elem_bytes) {
@@ -364,12 +368,17 @@ extern "C" int b200dp_gemm_bf16(const b200dp_gemm_args* a, void* stream) {
   return dispatch_major<__nv_bfloat16, 256>(a, s);
 }
 
-// Same contract with fp32 operands (A, B, mask_src fp32; D fp32): the tensor cores read them as TF32
-// (10-bit mantissa) and accumulate in fp32.  This is the path of `--dtype fp32` models that are too
+// Same contract with fp32 operands (A, B, mask_src fp32; D fp32), K-major only: the tensor cores read
+// them as TF32 (10-bit mantissa) and accumulate in fp32.  This is the path of `--dtype fp32` models that are too
 // large for the fused SIMT kernel - the reference trains in fp32 only (ref.py:159).
 extern "C" int b200dp_gemm_tf32(const b200dp_gemm_args* a, void* stream) {
   if (int rc = validate(a, 4)) return rc;
   B200DP_REQUIRE(a->d_fp32 != 0, "gemm_tf32: D must be fp32");
+  // Measured on B200: tcgen05.mma.kind::tf32 with a transposed (MN-major) operand leaves the accumulator
+  // untouched - TF32 operands are read K-major only (bf16 has no such limit).  Backward therefore works on
+  // transposed copies (b200dp_transpose_f32).
+  B200DP_REQUIRE(!a->a_mn_major && !a->b_mn_major,
+                 "gemm_tf32: kind::tf32 reads K-major operands only - pass transposed copies (b200dp_transpose_f32)");
   B200DP_REQUIRE(a->cta_group != 2, "gemm_tf32: the CTA-pair kernel is bf16 only");
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   if (a->tile_n == 128 || (a->tile_n == 0 && narrow_problem(a))) return dispatch_major<float, 128>(a, s);

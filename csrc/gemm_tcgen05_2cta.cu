@@ -36,7 +36,7 @@ constexpr int kBBytes = BNH * BK * 2;
 constexpr int kStageBytes = kABytes + kBBytes;
 constexpr int kBarrierOffset = kStages * kStageBytes;
 constexpr int kColsumOffset = kBarrierOffset + 256;
-constexpr int kSmemTotal = kColsumOffset + 4 * BN * 4 + 1024;
+constexpr int kSmemTotal = kColsumOffset + 2 * 4 * BN * 4 + 1024;
 
 // work unit -> tile (and which half of it, -1 = the whole tile)
 struct Unit { int m_blk, n_blk, half; };
@@ -119,7 +119,6 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   uint64_t* tmem_full = empty_bar + kStages;
   uint64_t* tmem_empty = tmem_full + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
-  int* cs_last = reinterpret_cast<int*>(tmem_slot + 1);
   float* cs_smem = reinterpret_cast<float*>(smem + kColsumOffset);
 
   const int warp = threadIdx.x >> 5;
@@ -249,9 +248,9 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         }
       };
       if (w.half < 0)
-        epilogue_tile<T, BN>(p, taddr, m0, w.n_blk * BN, w.n_blk, strip, quad, lane, cs_smem, cs_last, release);
+        epilogue_tile<T, BN>(p, taddr, m0, w.n_blk * BN, w.n_blk, strip, quad, lane, cs_smem, it & 1, release);
       else      // half tiles are never combined with the fused column sums (see launch_pair)
-        epilogue_tile<T, BN / 2>(p, taddr, m0, w.n_blk * BN + w.half * BNH, 0, strip, quad, lane, cs_smem, cs_last,
+        epilogue_tile<T, BN / 2>(p, taddr, m0, w.n_blk * BN + w.half * BNH, 0, strip, quad, lane, cs_smem, it & 1,
                                  release);
     }
   }

@@ -7,6 +7,10 @@
 //                     product path is the fused kernel in allreduce_sgd.cu.
 //  * cast_f32_bf16  - one-time input / weight conversion (the reference's per-step .float() cast,
 //                     ref.py:159, becomes a load-time cast).
+//  * transpose_f32  - dst[c, r] = src[r, c].  The fp32 (kind::tf32) GEMM path needs it: tcgen05 reads
+//                     TF32 operands K-major only (measured on B200: an MN-major kind::tf32 MMA leaves
+//                     the accumulator untouched), so backward's W^T, dY^T and X^T are materialised -
+//                     unlike the bf16 path, which expresses them in the UMMA descriptors.
 #include "common.cuh"
 
 namespace b200dp {
@@ -66,6 +70,26 @@ gather_rows_kernel(const uint4* __restrict__ src, long long src_ld16, const long
     const uint4* s = src + idx[r] * src_ld16;
     uint4* d = dst + (long long)r * row16;
     for (int c = lane; c < row16; c += 32) d[c] = __ldg(s + c);
+  }
+}
+
+// 32x32 tiles through padded shared memory: coalesced 128-byte reads along src rows and writes along dst rows
+__global__ void __launch_bounds__(256)
+transpose_f32_kernel(const float* __restrict__ src, long long lds, int rows, int cols, float* __restrict__ dst,
+                     long long ldd) {
+  __shared__ float tile[32][33];
+  const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;       // 32 x 8 threads
+#pragma unroll
+  for (int j = 0; j < 32; j += 8) {
+    const int r = r0 + ty + j, c = c0 + tx;
+    if (r < rows && c < cols) tile[ty + j][tx] = __ldg(src + (long long)r * lds + c);
+  }
+  __syncthreads();
+#pragma unroll
+  for (int j = 0; j < 32; j += 8) {
+    const int c = c0 + ty + j, r = r0 + tx;
+    if (r < rows && c < cols) dst[(long long)c * ldd + r] = tile[tx][ty + j];
   }
 }
 
@@ -139,6 +163,18 @@ extern "C" int b200dp_gather_rows(const void* src, long long src_row_bytes, cons
   gather_rows_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
       reinterpret_cast<const uint4*>(src), src_row_bytes / 16, idx, rows, int(row_bytes / 16),
       reinterpret_cast<uint4*>(dst));
+  B200DP_CUDA_OK(cudaGetLastError());
+  return B200DP_OK;
+}
+
+extern "C" int b200dp_transpose_f32(const float* src, long long lds, int rows, int cols, float* dst, long long ldd,
+                                    void* stream) {
+  B200DP_REQUIRE(src && dst, "transpose: null pointer");
+  B200DP_REQUIRE(rows > 0 && cols > 0 && lds >= cols && ldd >= rows, "transpose: bad shape (%d x %d, lds %lld, ldd %lld)",
+                 rows, cols, lds, ldd);
+  dim3 grid((cols + 31) / 32, (rows + 31) / 32);
+  B200DP_REQUIRE(grid.y <= 65535, "transpose: too many rows (%d)", rows);
+  transpose_f32_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(src, lds, rows, cols, dst, ldd);
   B200DP_CUDA_OK(cudaGetLastError());
   return B200DP_OK;
 }

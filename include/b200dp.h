@@ -72,8 +72,13 @@ int b200dp_gemm_bf16(const b200dp_gemm_args* args, void* stream);
 long long b200dp_gemm_colsum_scratch_bytes(int M, int N);
 /* Same contract with fp32 A, B and mask_src and an fp32 D: the tensor cores read the operands as TF32
  * (kind::tf32) and accumulate in fp32.  The reference computes in fp32 only (ref.py:159); this is the
- * path of fp32 models beyond the fused SIMT kernel.  lda/ldb/ldmask multiples of 4 elements. */
+ * path of fp32 models beyond the fused SIMT kernel.  lda/ldb/ldmask multiples of 4 elements.
+ * K-major operands only (a_mn_major = b_mn_major = 0): on B200 a kind::tf32 MMA with a transposed
+ * operand is a no-op, so backward passes transposed copies made with b200dp_transpose_f32. */
 int b200dp_gemm_tf32(const b200dp_gemm_args* args, void* stream);
+/* dst[c, r] = src[r, c] for an fp32 [rows, cols] matrix (leading dimensions in elements). */
+int b200dp_transpose_f32(const float* src, long long lds, int rows, int cols, float* dst, long long ldd,
+                         void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Whole-network SIMT kernel for MLPs too small for tensor cores (the reference's own 2-3-1 net,
@@ -163,6 +168,15 @@ int b200dp_cast_f32_bf16(const float* src, void* dst, long long n, void* stream)
  * is smaller than the shard (ref.py:146,155). */
 int b200dp_gather_rows(const void* src, long long src_row_bytes, const long long* idx, int rows,
                        long long row_bytes, void* dst, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Pinned host staging memory for input batches (the reference's DataLoader tensors never leave the
+ * CPU, ref.py:146,155; here every step's inputs cross PCIe).  2 MB-aligned anonymous memory advised to
+ * huge pages, touched, and registered with cudaHostRegister: measured 55.2-55.5 GB/s H2D on every
+ * allocation, where cudaHostAlloc / pin_memory() buffers vary between 45 and 55 GB/s.
+ */
+int b200dp_host_alloc(long long bytes, void** ptr, long long* mapped_bytes);
+int b200dp_host_free(void* ptr, long long mapped_bytes);
 
 /* ------------------------------------------------------------------------------------------------
  * Fused all-reduce + weighting + SGD-momentum over NVLink peer memory - the reference's

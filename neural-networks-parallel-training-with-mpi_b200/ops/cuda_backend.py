@@ -120,6 +120,14 @@ class GemmCompute:
         self.gemm_max_ctas = 0
         self.grad_scale = 1.0             # this rank's weight in the all-reduce, folded into dLoss/dYhat
         self._zero_targets = None
+        if cdt == torch.float32:
+            # kind::tf32 reads K-major operands only (an MN-major tf32 MMA is a no-op on B200), so the
+            # fp32 path materialises backward's transposes: W^T for dgrad, dY^T and X^T for wgrad
+            self.ldT = _align(R, 4)
+            self.xT = torch.empty(max(spec.sizes[:-1]) * self.ldT, dtype=cdt, device=dev)
+            self.dyT = torch.empty(max(spec.sizes[1:]) * self.ldT, dtype=cdt, device=dev)
+            self.wT = torch.empty(max([spec.sizes[l] * spec.sizes[l + 1] for l in range(1, self.L)], default=16),
+                                  dtype=cdt, device=dev)
 
     def prepare_batch(self, x, y):
         k_phys = self.spec.sizes[0]
@@ -167,8 +175,15 @@ class GemmCompute:
     def _dgrad(self, dy, l, a_in, out) -> None:
         """dLoss/d(input of layer l) with the ReLU mask of that input, and - fused into the epilogue -
         its column sums = the bias gradient of layer l-1 (the `sum` of AddmmBackward0, ref.py:176)."""
-        gemm.linear_dgrad(dy, self._w(l), a_in, out=out, max_ctas=self.gemm_max_ctas,
-                          colsum_out=self._gb(l - 1), colsum_scratch=self.gemm_cs_scratch)
+        kw = dict(out=out, max_ctas=self.gemm_max_ctas, colsum_out=self._gb(l - 1),
+                  colsum_scratch=self.gemm_cs_scratch)
+        w = self._w(l)
+        if self.cdt == torch.float32:
+            wT = self.wT[:w.numel()].view(w.shape[1], w.shape[0])
+            K.transpose_f32(w, wT)
+            gemm.gemm(dy, wT, out, mask_src=a_in, **{k: v for k, v in kw.items() if k != "out"})
+        else:
+            gemm.linear_dgrad(dy, w, a_in, **kw)
 
     def loss_and_grads(self, x, y) -> torch.Tensor:
         rows = x.shape[0]
@@ -222,8 +237,16 @@ class GemmCompute:
         strategy as soon as its GEMM is queued.  (db_l was written by the kernel that produced dY.)"""
         gw = self._gw(l)
         chunks = self.wgrad_chunks.get(l) or [(0, gw.shape[0])]
+        if self.cdt == torch.float32:
+            rows = dy.shape[0]
+            dyT = self.dyT[:dy.shape[1] * self.ldT].view(dy.shape[1], self.ldT)[:, :rows]
+            xT = self.xT[:a_in.shape[1] * self.ldT].view(a_in.shape[1], self.ldT)[:, :rows]
+            K.transpose_f32(dy, dyT)
+            K.transpose_f32(a_in, xT)
         for c, (r0, r1) in enumerate(chunks):
-            if len(chunks) == 1:
+            if self.cdt == torch.float32:
+                gemm.gemm(dyT[r0:r1], xT, gw[r0:r1], max_ctas=self.gemm_max_ctas)
+            elif len(chunks) == 1:
                 gemm.linear_wgrad(dy, a_in, out=gw, max_ctas=self.gemm_max_ctas)
             else:
                 gemm.linear_wgrad(dy[:, r0:r1], a_in, out=gw[r0:r1], max_ctas=self.gemm_max_ctas)

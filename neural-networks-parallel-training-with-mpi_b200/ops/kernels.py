@@ -31,6 +31,7 @@ _lib.register("b200dp_sgd_momentum", [c_void_p, c_void_p, c_int, c_void_p, c_voi
 _lib.register("b200dp_sgd_momentum_ex", [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_ll, c_float, c_float,
                                          c_float, c_int, c_int, c_void_p])
 _lib.register("b200dp_cast_f32_bf16", [c_void_p, c_void_p, c_ll, c_void_p])
+_lib.register("b200dp_transpose_f32", [c_void_p, c_ll, c_int, c_int, c_void_p, c_ll, c_void_p])
 _lib.register("b200dp_gather_rows", [c_void_p, c_ll, c_void_p, c_int, c_ll, c_void_p, c_void_p])
 
 
@@ -158,6 +159,17 @@ def sgd_momentum(params, grads, momentum, shadow, lr, mu, first_step, grad_scale
 def cast_f32_bf16(src, dst, stream=None):
     _lib.check(L().b200dp_cast_f32_bf16(src.data_ptr(), dst.data_ptr(), src.numel(), _lib.stream_ptr(stream)))
     _lib.count()
+
+
+def transpose_f32(src, dst, stream=None):
+    """``dst[c, r] = src[r, c]``; both 2-D fp32 with unit inner stride (row strides are honoured)."""
+    rows, cols = src.shape
+    assert src.dtype == dst.dtype == torch.float32 and tuple(dst.shape) == (cols, rows)
+    assert src.stride(1) == 1 and dst.stride(1) == 1
+    _lib.check(L().b200dp_transpose_f32(src.data_ptr(), src.stride(0), rows, cols, dst.data_ptr(), dst.stride(0),
+                                        _lib.stream_ptr(stream)))
+    _lib.count()
+    return dst
 
 
 def gather_rows(src, idx, dst=None, stream=None):

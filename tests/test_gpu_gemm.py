@@ -182,13 +182,18 @@ def test_tf32_forward(M, N, K, tile_n):
 
 @pytest.mark.parametrize("M,N,K", [(128, 256, 64), (512, 256, 384), (200, 136, 72), (2048, 2048, 1024)])
 def test_tf32_dgrad_with_colsum(M, N, K):
-    from b200dp.ops import gemm
+    """kind::tf32 reads K-major operands only: dgrad runs on a transposed copy of W."""
+    from b200dp.ops import gemm, kernels as Kk
     torch.manual_seed(8)
     dy, w = _rand((M, N), dtype=torch.float32), _rand((N, K), N ** -0.5, dtype=torch.float32)
     x = torch.relu(_rand((M, K), dtype=torch.float32))
+    wT = torch.empty(K, N, device="cuda")
+    Kk.transpose_f32(w, wT)
+    assert torch.equal(wT, w.t())
     scratch = torch.zeros(gemm.colsum_scratch_bytes(M, K), dtype=torch.uint8, device="cuda")
     cs = torch.empty(K, device="cuda")
-    got = gemm.linear_dgrad(dy, w, x, colsum_out=cs, colsum_scratch=scratch)
+    got = torch.empty(M, K, device="cuda")
+    gemm.gemm(dy, wT, got, mask_src=x, colsum_out=cs, colsum_scratch=scratch)
     want = (dy @ w) * (x > 0)
     _close_tf32(got, want)
     torch.testing.assert_close(cs, want.sum(0), rtol=5e-3, atol=4e-3 * float(want.sum(0).abs().max()))
@@ -196,9 +201,29 @@ def test_tf32_dgrad_with_colsum(M, N, K):
 
 @pytest.mark.parametrize("M,N,K", [(128, 256, 64), (512, 256, 384), (328, 136, 72), (4096, 1024, 2048)])
 def test_tf32_wgrad(M, N, K):
-    from b200dp.ops import gemm
+    from b200dp.ops import gemm, kernels as Kk
     torch.manual_seed(9)
     dy, x = _rand((M, N), M ** -0.5, dtype=torch.float32), _rand((M, K), dtype=torch.float32)
+    dyT, xT = torch.empty(N, M, device="cuda"), torch.empty(K, M, device="cuda")
+    Kk.transpose_f32(dy, dyT)
+    Kk.transpose_f32(x, xT)
     out = torch.empty(N, K, device="cuda")
-    got = gemm.linear_wgrad(dy, x, out=out)
-    _close_tf32(got, dy.t() @ x)
+    gemm.gemm(dyT, xT, out)
+    _close_tf32(out, dy.t() @ x)
+
+
+def test_tf32_refuses_transposed_operands():
+    from b200dp.ops import gemm
+    from b200dp.ops._lib import B200dpError
+    a, b = _rand((64, 128), dtype=torch.float32), _rand((64, 256), dtype=torch.float32)
+    with pytest.raises(B200dpError, match="K-major"):
+        gemm.gemm(a, b, torch.empty(128, 256, device="cuda"), a_mn_major=True, b_mn_major=True)
+
+
+@pytest.mark.parametrize("rows,cols", [(32, 32), (100, 36), (1000, 776), (4096, 2048)])
+def test_transpose_f32(rows, cols):
+    from b200dp.ops import kernels as Kk
+    src = torch.randn(rows, cols + 4, device="cuda")[:, :cols]           # strided source
+    dst = torch.empty(cols, rows + 4, device="cuda")[:, :rows]           # strided destination
+    Kk.transpose_f32(src, dst)
+    assert torch.equal(dst, src.t())

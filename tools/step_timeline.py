@@ -16,7 +16,7 @@ def main():
     ap.add_argument("--config", default="wide")
     a = ap.parse_args()
     args = argparse.Namespace(config=a.config, sync="auto", rows_per_gpu=None, no_overlap=False, bucket_mb=0.0)
-    t = bench.make_trainer(args, bench.CONFIGS[a.config], 0, 1)
+    t = bench.make_trainer(args, bench.CONFIGS[a.config], a.config, 1)
     for _ in range(5):
         t.step(t.x, t.y)
     torch.cuda.synchronize()
