@@ -70,10 +70,15 @@ __device__ __forceinline__ bool peer_barrier(const SyncArgs& a, int block, uint3
   if (t < a.world) {
     red_release_sys_add(a.flags[t] + block * B200DP_MAX_RANKS + a.rank, 1u);
     const uint32_t* mine = a.flags[a.rank] + block * B200DP_MAX_RANKS + t;
+    // Wait politely: relaxed loads with a growing sleep in between, ONE acquire fence at the end.  This
+    // kernel shares its SMs with backward's GEMMs; a tight ld.acquire.sys spin (the first version)
+    // slowed every GEMM on the GPU by half for as long as a single block was waiting for a peer.
     uint64_t t0 = 0;
-    uint32_t spins = 0;
-    while (int32_t(ld_acquire_sys(mine) - target) < 0) {
-      if ((++spins & 0xfff) == 0) {
+    uint32_t spins = 0, sleep_ns = 32;
+    while (int32_t(ld_relaxed_sys(mine) - target) < 0) {
+      __nanosleep(sleep_ns);
+      if (sleep_ns < 1024) sleep_ns <<= 1;
+      if ((++spins & 0x3f) == 0) {
         const uint64_t now = global_timer_ns();
         if (t0 == 0) t0 = now;
         else if (a.timeout_ns && now - t0 > a.timeout_ns) {
@@ -83,6 +88,7 @@ __device__ __forceinline__ bool peer_barrier(const SyncArgs& a, int block, uint3
         }
       }
     }
+    fence_acq_rel_sys();
   }
   return __syncthreads_or(timed_out) == 0;
 }
@@ -91,7 +97,7 @@ template <typename G> struct Vec;
 template <> struct Vec<float> {
   static constexpr int N = 4;
   __device__ static uint4 load(const void* base, long long i) {
-    return *reinterpret_cast<const uint4*>(reinterpret_cast<const float*>(base) + i);
+    return __ldcs(reinterpret_cast<const uint4*>(reinterpret_cast<const float*>(base) + i));
   }
   __device__ static void unpack(const uint4& v, float (&o)[4]) {
     o[0] = __uint_as_float(v.x); o[1] = __uint_as_float(v.y); o[2] = __uint_as_float(v.z); o[3] = __uint_as_float(v.w);
@@ -100,7 +106,7 @@ template <> struct Vec<float> {
 template <> struct Vec<__nv_bfloat16> {
   static constexpr int N = 8;
   __device__ static uint4 load(const void* base, long long i) {
-    return *reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(base) + i);
+    return __ldcs(reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(base) + i));
   }
   __device__ static void unpack(const uint4& v, float (&o)[8]) {
     o[0] = bf16_lo(v.x); o[1] = bf16_hi(v.x); o[2] = bf16_lo(v.y); o[3] = bf16_hi(v.y);
@@ -137,66 +143,81 @@ __device__ __forceinline__ void reduce_raw(const SyncArgs& a, const uint4 (&raw)
   for (int j = 0; j < VN; ++j) acc[j] = acc[j] / a.div;
 }
 
-// NVLS: the switch adds the N copies; one instruction returns the sum
+// NVLS: the switch adds the N copies; one instruction returns the sum (kept packed until consumed)
 template <typename G>
-__device__ __forceinline__ void nvls_reduce_vec(const SyncArgs& a, long long i, float (&acc)[Vec<G>::N]);
+__device__ __forceinline__ uint4 nvls_load_vec(const SyncArgs& a, long long i);
 template <>
-__device__ __forceinline__ void nvls_reduce_vec<float>(const SyncArgs& a, long long i, float (&acc)[4]) {
+__device__ __forceinline__ uint4 nvls_load_vec<float>(const SyncArgs& a, long long i) {
   const float* p = reinterpret_cast<const float*>(a.mc_grads) + i;
+  uint4 v;
   asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
-               : "=f"(acc[0]), "=f"(acc[1]), "=f"(acc[2]), "=f"(acc[3]) : "l"(p) : "memory");
-#pragma unroll
-  for (int j = 0; j < 4; ++j) acc[j] = acc[j] / a.div;
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
 }
 template <>
-__device__ __forceinline__ void nvls_reduce_vec<__nv_bfloat16>(const SyncArgs& a, long long i, float (&acc)[8]) {
+__device__ __forceinline__ uint4 nvls_load_vec<__nv_bfloat16>(const SyncArgs& a, long long i) {
   const __nv_bfloat16* p = reinterpret_cast<const __nv_bfloat16*>(a.mc_grads) + i;
-  uint32_t x, y, z, w;
+  uint4 v;
   asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
-               : "=r"(x), "=r"(y), "=r"(z), "=r"(w) : "l"(p) : "memory");
-  acc[0] = bf16_lo(x); acc[1] = bf16_hi(x); acc[2] = bf16_lo(y); acc[3] = bf16_hi(y);
-  acc[4] = bf16_lo(z); acc[5] = bf16_hi(z); acc[6] = bf16_lo(w); acc[7] = bf16_hi(w);
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
+template <typename G>
+__device__ __forceinline__ void nvls_finish_vec(const SyncArgs& a, const uint4& v, float (&acc)[Vec<G>::N]) {
+  Vec<G>::unpack(v, acc);
 #pragma unroll
-  for (int j = 0; j < 8; ++j) acc[j] = acc[j] / a.div;
+  for (int j = 0; j < Vec<G>::N; ++j) acc[j] = acc[j] / a.div;
+}
+
+// momentum / master values of one vector, loaded up front together with the gradients (streaming
+// loads: keep the GEMMs' panels in L2)
+template <int VN>
+__device__ __forceinline__ void load_state(const SyncArgs& a, long long i, float4 (&m4)[VN / 4], float4 (&p4)[VN / 4]) {
+#pragma unroll
+  for (int j = 0; j < VN / 4; ++j) {
+    if (!a.first) m4[j] = __ldcs(reinterpret_cast<const float4*>(a.momentum + i) + j);
+    p4[j] = __ldcs(reinterpret_cast<const float4*>(a.params[a.rank] + i) + j);
+  }
 }
 
 template <int VN>
-__device__ __forceinline__ void sgd_vec(const SyncArgs& a, long long i, const float (&g)[VN], float (&p)[VN]) {
+__device__ __forceinline__ void sgd_vec(const SyncArgs& a, long long i, const float (&g)[VN], float4 (&m4)[VN / 4],
+                                        float4 (&p4)[VN / 4], float (&p)[VN]) {
   float* mom = a.momentum + i;
-  float* par = a.params[a.rank] + i;
 #pragma unroll
-  for (int j = 0; j < VN; j += 4) {
-    float4 m4;
-    if (a.first) m4 = make_float4(g[j], g[j + 1], g[j + 2], g[j + 3]);
+  for (int j = 0; j < VN / 4; ++j) {
+    float4 m = m4[j];
+    const int e = 4 * j;
+    if (a.first) m = make_float4(g[e], g[e + 1], g[e + 2], g[e + 3]);
     else {
-      m4 = __ldcs(reinterpret_cast<const float4*>(mom + j));
-      m4.x = fmaf(a.mu, m4.x, g[j]); m4.y = fmaf(a.mu, m4.y, g[j + 1]);
-      m4.z = fmaf(a.mu, m4.z, g[j + 2]); m4.w = fmaf(a.mu, m4.w, g[j + 3]);
+      m.x = fmaf(a.mu, m.x, g[e]); m.y = fmaf(a.mu, m.y, g[e + 1]);
+      m.z = fmaf(a.mu, m.z, g[e + 2]); m.w = fmaf(a.mu, m.w, g[e + 3]);
     }
-    __stcs(reinterpret_cast<float4*>(mom + j), m4);      // streaming: keep the GEMMs' panels in L2
-    float4 p4 = __ldcs(reinterpret_cast<const float4*>(par + j));
-    p4.x -= a.lr * m4.x; p4.y -= a.lr * m4.y; p4.z -= a.lr * m4.z; p4.w -= a.lr * m4.w;
-    p[j] = p4.x; p[j + 1] = p4.y; p[j + 2] = p4.z; p[j + 3] = p4.w;
+    __stcs(reinterpret_cast<float4*>(mom) + j, m);
+    float4 q = p4[j];
+    q.x -= a.lr * m.x; q.y -= a.lr * m.y; q.z -= a.lr * m.z; q.w -= a.lr * m.w;
+    p[e] = q.x; p[e + 1] = q.y; p[e + 2] = q.z; p[e + 3] = q.w;
   }
 }
 
 template <int VN>
 __device__ __forceinline__ void store_master(float* dst, const float (&p)[VN]) {
 #pragma unroll
-  for (int j = 0; j < VN; j += 4) *reinterpret_cast<float4*>(dst + j) = make_float4(p[j], p[j + 1], p[j + 2], p[j + 3]);
+  for (int j = 0; j < VN; j += 4) __stcs(reinterpret_cast<float4*>(dst + j), make_float4(p[j], p[j + 1], p[j + 2], p[j + 3]));
 }
 template <int VN>
 __device__ __forceinline__ void store_shadow(__nv_bfloat16* dst, const float (&p)[VN]) {
   if constexpr (VN == 8) {
-    *reinterpret_cast<uint4*>(dst) = make_uint4(pack_bf16x2(p[0], p[1]), pack_bf16x2(p[2], p[3]),
-                                                pack_bf16x2(p[4], p[5]), pack_bf16x2(p[6], p[7]));
+    __stcs(reinterpret_cast<uint4*>(dst), make_uint4(pack_bf16x2(p[0], p[1]), pack_bf16x2(p[2], p[3]),
+                                                     pack_bf16x2(p[4], p[5]), pack_bf16x2(p[6], p[7])));
   } else {
-    *reinterpret_cast<uint2*>(dst) = make_uint2(pack_bf16x2(p[0], p[1]), pack_bf16x2(p[2], p[3]));
+    __stcs(reinterpret_cast<uint2*>(dst), make_uint2(pack_bf16x2(p[0], p[1]), pack_bf16x2(p[2], p[3])));
   }
 }
 
-// WR = compile-time ceiling of the world size (2, 4 or 8), U = vectors in flight per thread; the
-// launcher picks U*WR = 16, i.e. sixteen 16-byte loads outstanding per thread whatever the world.
+// WR = compile-time ceiling of the world size (2, 4 or 8), U = vectors in flight per thread: U*(WR + 4)
+// 16-byte loads (gradients of every rank + momentum + master) are outstanding per thread, sized so the
+// kernel stays within 128 registers (one sync CTA must fit beside a persistent GEMM CTA).
 template <typename G, int WR, int U>
 __device__ void sync_body(const SyncArgs& a, int block, int nblocks) {
   constexpr int VN = Vec<G>::N;
@@ -215,24 +236,18 @@ __device__ void sync_body(const SyncArgs& a, int block, int nblocks) {
   const bool has_shadow = a.shadow[a.rank] != nullptr;
   const long long step = (long long)nblocks * blockDim.x * U;
   for (long long u0 = u_lo + (long long)block * blockDim.x * U + threadIdx.x; u0 < u_hi; u0 += step) {
-    float g[U][VN];
-    if (a.mode == 2) {
+    // Every load of this round is issued before anything is consumed: the peers' gradients (NVLink round
+    // trips), and the local momentum / master values the update needs - they do not depend on one
+    // another, and with one CTA per SM memory-level parallelism is what sets the rate.
+    uint4 raw[U][WR];
+    float4 m4[U][VN / 4], p4[U][VN / 4];
 #pragma unroll
-      for (int k = 0; k < U; ++k) {
-        const long long u = u0 + (long long)k * blockDim.x;
-        if (u < u_hi) nvls_reduce_vec<G>(a, u * VN, g[k]);
-      }
-    } else {
-      uint4 raw[U][WR];
-#pragma unroll
-      for (int k = 0; k < U; ++k) {
-        const long long u = u0 + (long long)k * blockDim.x;
-        if (u < u_hi) load_all_ranks<G, WR>(a, u * VN, raw[k]);
-      }
-#pragma unroll
-      for (int k = 0; k < U; ++k) {
-        const long long u = u0 + (long long)k * blockDim.x;
-        if (u < u_hi) reduce_raw<G, WR>(a, raw[k], g[k]);
+    for (int k = 0; k < U; ++k) {
+      const long long u = u0 + (long long)k * blockDim.x;
+      if (u < u_hi) {
+        if (a.mode == 2) raw[k][0] = nvls_load_vec<G>(a, u * VN);
+        else load_all_ranks<G, WR>(a, u * VN, raw[k]);
+        load_state<VN>(a, u * VN, m4[k], p4[k]);
       }
     }
 #pragma unroll
@@ -240,8 +255,10 @@ __device__ void sync_body(const SyncArgs& a, int block, int nblocks) {
       const long long u = u0 + (long long)k * blockDim.x;
       if (u >= u_hi) continue;
       const long long i = u * VN;
-      float p[VN];
-      sgd_vec<VN>(a, i, g[k], p);
+      float g[VN], p[VN];
+      if (a.mode == 2) nvls_finish_vec<G>(a, raw[k][0], g);
+      else reduce_raw<G, WR>(a, raw[k], g);
+      sgd_vec<VN>(a, i, g, m4[k], p4[k], p);
       store_master<VN>(a.params[a.rank] + i, p);
       // fp32 values that kernels read straight from the master buffer (the biases: they sit at the end
       // of a layer's bucket) must be identical on every rank, not only on the owner of their slice
@@ -299,8 +316,8 @@ sync_emulated_kernel(const SyncArgs* __restrict__ all) {
 
 template <typename G>
 const void* pick_kernel(int world, bool emulated) {
-  if (world <= 2) return emulated ? (const void*)sync_emulated_kernel<G, 2, 6> : (const void*)sync_kernel<G, 2, 6>;
-  if (world <= 4) return emulated ? (const void*)sync_emulated_kernel<G, 4, 4> : (const void*)sync_kernel<G, 4, 4>;
+  if (world <= 2) return emulated ? (const void*)sync_emulated_kernel<G, 2, 4> : (const void*)sync_kernel<G, 2, 4>;
+  if (world <= 4) return emulated ? (const void*)sync_emulated_kernel<G, 4, 3> : (const void*)sync_kernel<G, 4, 3>;
   return emulated ? (const void*)sync_emulated_kernel<G, 8, 2> : (const void*)sync_kernel<G, 8, 2>;
 }
 
@@ -393,6 +410,21 @@ int pick_blocks(const b200dp_sync_args* in) {
 }
 
 }  // namespace
+
+int sync_regs_per_cta() {
+  int best = -1;
+  const void* ks[] = {pick_kernel<__nv_bfloat16>(2, false), pick_kernel<__nv_bfloat16>(4, false),
+                      pick_kernel<__nv_bfloat16>(8, false), pick_kernel<float>(2, false),
+                      pick_kernel<float>(4, false), pick_kernel<float>(8, false)};
+  for (const void* k : ks) {
+    cudaFuncAttributes at;
+    if (cudaFuncGetAttributes(&at, k) != cudaSuccess) return -1;
+    const int v = ((at.numRegs * 32 + 255) / 256) * 256 * (kSyncThreads / 32);
+    if (v > best) best = v;
+  }
+  return best;
+}
+
 }  // namespace b200dp
 
 using namespace b200dp;

@@ -14,6 +14,13 @@ namespace b200dp {
 constexpr int kGemmBM = 128;          // rows of D per CTA (= TMEM lanes)
 constexpr int kGemmThreads = 192;     // warp 0 TMA producer, warp 1 MMA issuer, warps 2..5 epilogue
 constexpr int kEpiThreads = 128;
+// Register budget of the GEMM kernels.  A persistent GEMM CTA (192 threads) must leave room on its SM
+// for one CTA of the fused gradient sync (256 threads x 128 registers = 32 K of the SM's 64 K
+// registers): the sync kernels run on a second stream WHILE backward's GEMMs run, and their cross-GPU
+// barrier needs all of their CTAs resident at once.  __launch_bounds__(192, 2) makes ptxas stay within
+// half of the register file (<= 168 registers/thread, 31.5 K per CTA); shared memory still limits the
+// GEMM itself to one CTA per SM.
+constexpr int kGemmMinCtas = 2;
 constexpr int kEpiBarrierId = 1;      // named barrier of the four epilogue warps
 
 // ---- element traits ---------------------------------------------------------------------------

@@ -30,7 +30,7 @@ namespace {
 constexpr int BM = kGemmBM;    // UMMA M (cta_group::1)
 constexpr int kStages = 4;
 
-template <typename T, int BN>
+template <typename T, int BN, bool A_MN>
 struct Smem {
   static constexpr int BK = Elem<T>::BK;
   static constexpr int kABytes = BM * 128;          // BM rows x one 128-byte swizzle row of K
@@ -38,13 +38,17 @@ struct Smem {
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kBarrierOffset = kStages * kStageBytes;
   static constexpr int kColsumOffset = kBarrierOffset + 256;
-  static constexpr int kTotal = kColsumOffset + 2 * 4 * BN * 4 + 1024;   // + alignment slack
+  // column sums are fused into GEMMs whose A operand is K-major (dgrad; wgrad never asks for them):
+  // keeping the staging out of the wgrad instantiation keeps it within the 196 KB shared-memory
+  // carve-out, i.e. leaves 60 KB of L1 to the kernels that run beside it (see gemm_tcgen05_2cta.cu)
+  static constexpr int kColsumBytes = A_MN ? 0 : 2 * 4 * BN * 4;
+  static constexpr int kTotal = kColsumOffset + kColsumBytes + 1024;   // + alignment slack
 };
 
 template <typename T, int BN, bool A_MN, bool B_MN>
-__global__ void __launch_bounds__(kGemmThreads, 1)
+__global__ void __launch_bounds__(kGemmThreads, kGemmMinCtas)
 gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
-  using S = Smem<T, BN>;
+  using S = Smem<T, BN, A_MN>;
   constexpr int BK = Elem<T>::BK;
   constexpr int UMMA_K = Elem<T>::UMMA_K;
   constexpr int E = 128 / Elem<T>::kBytes;          // elements per swizzle row (= BK)
@@ -183,7 +187,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 
 template <typename T, int BN, bool A_MN, bool B_MN>
 int launch(const b200dp_gemm_args* a, cudaStream_t stream) {
-  using S = Smem<T, BN>;
+  using S = Smem<T, BN, A_MN>;
   constexpr int BK = Elem<T>::BK;
   constexpr int EB = Elem<T>::kBytes;
   CUtensorMap tmA, tmB;
@@ -197,6 +201,7 @@ int launch(const b200dp_gemm_args* a, cudaStream_t stream) {
   else rc = get_tensor_map(&tmB, Elem<T>::kTma, EB, a->B, a->N, a->K, a->ldb, BN);
   if (rc) return rc;
 
+  B200DP_REQUIRE(a->colsum_out == nullptr || !A_MN, "gemm: column sums need a K-major A operand");
   GemmParams p;
   fill_gemm_params(a, &p);
   p.num_m_blocks = (a->M + BM - 1) / BM;
@@ -344,6 +349,18 @@ void fill_gemm_params(const b200dp_gemm_args* a, GemmParams* p) {
 }
 
 int gemm_pair_dispatch(const b200dp_gemm_args* a, cudaStream_t s);   // gemm_tcgen05_2cta.cu
+int gemm_pair_regs_per_cta();                                           // gemm_tcgen05_2cta.cu
+int sync_regs_per_cta();                                                // allreduce_sgd.cu
+
+namespace {
+template <typename Kern>
+int regs_per_cta(Kern k, int threads) {
+  cudaFuncAttributes at;
+  if (cudaFuncGetAttributes(&at, k) != cudaSuccess) return -1;
+  const int per_warp = ((at.numRegs * 32 + 255) / 256) * 256;     // allocation granularity: 256 registers per warp
+  return per_warp * (threads / 32);
+}
+}  // namespace
 
 }  // namespace b200dp
 
@@ -383,4 +400,28 @@ extern "C" int b200dp_gemm_tf32(const b200dp_gemm_args* a, void* stream) {
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   if (a->tile_n == 128 || (a->tile_n == 0 && narrow_problem(a))) return dispatch_major<float, 128>(a, s);
   return dispatch_major<float, 256>(a, s);
+}
+
+// Registers one GEMM CTA and one fused-sync CTA occupy on an SM.  Their sum must stay within the SM's
+// 65536 registers or the sync kernels cannot run beside backward's GEMMs (see kGemmMinCtas).
+extern "C" int b200dp_overlap_register_budget(int* gemm_regs_per_cta, int* sync_regs_per_cta_out) {
+  B200DP_REQUIRE(gemm_regs_per_cta && sync_regs_per_cta_out, "register_budget: null pointer");
+  int g = gemm_pair_regs_per_cta();
+  const int cands[] = {
+      regs_per_cta(gemm_kernel<__nv_bfloat16, 256, false, false>, kGemmThreads),
+      regs_per_cta(gemm_kernel<__nv_bfloat16, 256, false, true>, kGemmThreads),
+      regs_per_cta(gemm_kernel<__nv_bfloat16, 256, true, true>, kGemmThreads),
+      regs_per_cta(gemm_kernel<__nv_bfloat16, 128, false, false>, kGemmThreads),
+      regs_per_cta(gemm_kernel<__nv_bfloat16, 128, false, true>, kGemmThreads),
+      regs_per_cta(gemm_kernel<__nv_bfloat16, 128, true, true>, kGemmThreads),
+      regs_per_cta(gemm_kernel<float, 256, false, false>, kGemmThreads),
+      regs_per_cta(gemm_kernel<float, 128, false, false>, kGemmThreads)};
+  for (int c : cands) {
+    B200DP_REQUIRE(c > 0, "register_budget: cudaFuncGetAttributes failed");
+    if (c > g) g = c;
+  }
+  *gemm_regs_per_cta = g;
+  *sync_regs_per_cta_out = sync_regs_per_cta();
+  B200DP_REQUIRE(g > 0 && *sync_regs_per_cta_out > 0, "register_budget: cudaFuncGetAttributes failed");
+  return B200DP_OK;
 }

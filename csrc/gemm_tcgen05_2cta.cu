@@ -29,14 +29,26 @@ constexpr int BN = 256;        // columns per pair
 constexpr int BNH = 128;       // B columns staged by each CTA
 constexpr int BK = Elem<T>::BK;
 constexpr int UMMA_K = Elem<T>::UMMA_K;
-constexpr int kStages = 6;
-
 constexpr int kABytes = BM * BK * 2;
 constexpr int kBBytes = BNH * BK * 2;
 constexpr int kStageBytes = kABytes + kBBytes;
-constexpr int kBarrierOffset = kStages * kStageBytes;
-constexpr int kColsumOffset = kBarrierOffset + 256;
-constexpr int kSmemTotal = kColsumOffset + 2 * 4 * BN * 4 + 1024;
+
+// Depth of the TMA ring.  Forward GEMMs (both operands K-major) run alone and take 6 stages (192 KB).
+// Backward's GEMMs (dgrad, wgrad: an MN-major operand) run BESIDE the gradient-sync / update kernels
+// of the layers above; those kernels live on ordinary loads whose in-flight data sits in L1, and L1 is
+// what the SM has left after the shared-memory carve-out.  With 6 stages + the column-sum staging the
+// GEMM needed the 228 KB carve-out (28 KB of L1): the co-running sync kernel crawled and dragged the
+// GEMM with it (2-GPU step 3.59 ms).  5 stages fit the 196 KB carve-out (60 KB of L1): 3.44 ms, for
+// +0.5 % on a GEMM that runs alone.
+template <bool A_MN, bool B_MN>
+struct PairSmem {
+  static constexpr int kStages = (A_MN || B_MN) ? 5 : 6;
+  static constexpr int kBarrierOffset = kStages * kStageBytes;
+  static constexpr int kColsumOffset = kBarrierOffset + 256;
+  // the column sums are fused into dgrad only (A K-major, B MN-major)
+  static constexpr int kColsumBytes = (!A_MN && B_MN) ? 2 * 4 * BN * 4 : 0;
+  static constexpr int kTotal = kColsumOffset + kColsumBytes + 1024;
+};
 
 // work unit -> tile (and which half of it, -1 = the whole tile)
 struct Unit { int m_blk, n_blk, half; };
@@ -109,9 +121,13 @@ __device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {
 }
 
 template <bool A_MN, bool B_MN>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, kGemmMinCtas)
 gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                       const __grid_constant__ CUtensorMap tmBh, const GemmParams p) {
+  using S = PairSmem<A_MN, B_MN>;
+  constexpr int kStages = S::kStages;
+  constexpr int kBarrierOffset = S::kBarrierOffset;
+  constexpr int kColsumOffset = S::kColsumOffset;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + kBarrierOffset);
@@ -287,6 +303,8 @@ int launch_pair(const b200dp_gemm_args* a, cudaStream_t stream) {
   // tickets count whole 256-column blocks)
   p.full_tiles = tiles;
   const int rem = tiles % clusters;
+  B200DP_REQUIRE(a->colsum_out == nullptr || (!A_MN && B_MN),
+                 "gemm: the CTA-pair kernel fuses column sums into dgrad (A K-major, B MN-major) only");
   if (a->split_tail >= 0 && tiles > clusters && rem > 0 && 2 * rem <= clusters && a->colsum_out == nullptr)
     p.full_tiles = tiles - rem;
   tmBh = tmB;
@@ -298,6 +316,7 @@ int launch_pair(const b200dp_gemm_args* a, cudaStream_t stream) {
   if (clusters > units) clusters = units;
   auto kern = gemm_bf16_pair_kernel<A_MN, B_MN>;
   static bool attr_done[64] = {false};
+  constexpr int kSmemTotal = PairSmem<A_MN, B_MN>::kTotal;
   if (int e = ensure_smem_attr(kern, kSmemTotal, attr_done)) return e;
   kern<<<2 * clusters, kGemmThreads, kSmemTotal, stream>>>(tmA, tmB, tmBh, p);
   B200DP_CUDA_OK(cudaGetLastError());
@@ -305,6 +324,19 @@ int launch_pair(const b200dp_gemm_args* a, cudaStream_t stream) {
 }
 
 }  // namespace
+
+int gemm_pair_regs_per_cta() {
+  int best = -1;
+  const void* ks[] = {(const void*)gemm_bf16_pair_kernel<false, false>, (const void*)gemm_bf16_pair_kernel<false, true>,
+                      (const void*)gemm_bf16_pair_kernel<true, true>, (const void*)gemm_bf16_pair_kernel<true, false>};
+  for (const void* k : ks) {
+    cudaFuncAttributes at;
+    if (cudaFuncGetAttributes(&at, k) != cudaSuccess) return -1;
+    const int v = ((at.numRegs * 32 + 255) / 256) * 256 * (kGemmThreads / 32);
+    if (v > best) best = v;
+  }
+  return best;
+}
 
 // called from b200dp_gemm_bf16 (gemm_tcgen05.cu) after argument validation
 int gemm_pair_dispatch(const b200dp_gemm_args* a, cudaStream_t s) {

@@ -60,6 +60,8 @@ typedef struct b200dp_gemm_args {
   /* Fused bias gradient (the `sum` of AddmmBackward0, ref.py:176): when colsum_out is set the
    * epilogue also writes colsum_out[n] = sum_m D[m,n] (the values it stores, before rounding), i.e.
    * the db of the layer whose dY this GEMM produces.  Fixed summation order (bit-reproducible).
+   * Needs a K-major A (a_mn_major = 0); the CTA-pair kernel fuses it into the dgrad layout only
+   * (a_mn_major = 0, b_mn_major = 1) - other layouts take the one-CTA kernel (cta_group = 1).
    * colsum_scratch: b200dp_gemm_colsum_scratch_bytes(M, N) bytes whose first 4096 bytes are zero
    * before the first use (ticket counters; every launch leaves them zero). */
   void* colsum_out;     /* bf16 or fp32 [N], or NULL */
@@ -70,6 +72,9 @@ typedef struct b200dp_gemm_args {
 
 int b200dp_gemm_bf16(const b200dp_gemm_args* args, void* stream);
 long long b200dp_gemm_colsum_scratch_bytes(int M, int N);
+/* Registers that one persistent GEMM CTA and one fused-sync CTA occupy on an SM.  The step schedule runs
+ * the sync kernels beside backward's GEMMs, so gemm + sync must fit the SM's 65536 registers. */
+int b200dp_overlap_register_budget(int* gemm_regs_per_cta, int* sync_regs_per_cta);
 /* Same contract with fp32 A, B and mask_src and an fp32 D: the tensor cores read the operands as TF32
  * (kind::tf32) and accumulate in fp32.  The reference computes in fp32 only (ref.py:159); this is the
  * path of fp32 models beyond the fused SIMT kernel.  lda/ldb/ldmask multiples of 4 elements.

@@ -99,6 +99,86 @@ def pcie_closeness() -> Optional[List[List[int]]]:
     return score if ok else None
 
 
+_PROBE_SRC = r"""
+import json, sys, torch
+n = torch.cuda.device_count()
+nbytes = 48 << 20
+host, dev, st = [], [], []
+for i in range(n):
+    torch.cuda.set_device(i)
+    host.append(torch.empty(nbytes, dtype=torch.uint8).pin_memory())
+    dev.append(torch.empty(nbytes, dtype=torch.uint8, device=f"cuda:{i}"))
+    st.append(torch.cuda.Stream(device=i))
+def run(ids, reps=3):
+    best = {i: 1e9 for i in ids}
+    for _ in range(reps):
+        ev = {}
+        for i in ids:
+            torch.cuda.set_device(i)
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            with torch.cuda.stream(st[i]):
+                a.record(st[i]); dev[i].copy_(host[i], non_blocking=True); dev[i].copy_(host[i], non_blocking=True); b.record(st[i])
+            ev[i] = (a, b)
+        for i in ids:
+            torch.cuda.set_device(i); st[i].synchronize()
+            best[i] = min(best[i], ev[i][0].elapsed_time(ev[i][1]))
+    return best
+for i in range(n):
+    run([i], 1)
+alone = {i: run([i])[i] for i in range(n)}
+score = [[0] * n for _ in range(n)]
+for i in range(n):
+    for j in range(i + 1, n):
+        t = run([i, j])
+        slow = max(t[i] / alone[i], t[j] / alone[j])
+        score[i][j] = score[j][i] = int(round(100 * max(slow - 1.0, 0.0)))
+json.dump({"alone_ms": alone, "closeness": score}, sys.stdout)
+"""
+
+
+def measured_pcie_closeness(timeout_s: float = 90.0) -> Optional[List[List[int]]]:
+    """Where the PCIe topology is not visible (virtualised hosts give every GPU its own root complex and
+    NVML reports every pair as "same node"), find out by measurement which GPUs share a host uplink:
+    a pair whose simultaneous pinned H2D copies slow each other down shares one.  Entry = percent
+    slowdown of the pair's copies against each GPU copying alone.  Runs once per job, in a short-lived
+    child process of local rank 0 (so no rank keeps CUDA contexts on GPUs it does not use); the other
+    local ranks read the result from a file keyed by the launcher's pid."""
+    import json
+    import subprocess
+    import sys
+    import tempfile
+    import time
+
+    local_rank = _first_int(os.environ, "LOCAL_RANK", "OMPI_COMM_WORLD_LOCAL_RANK", "MPI_LOCALRANKID", "SLURM_LOCALID") or 0
+    key = f"b200dp_pcie_{os.getppid()}_{os.environ.get('MASTER_PORT', '0')}.json"
+    path = os.path.join(tempfile.gettempdir(), key)
+    if local_rank == 0:
+        result = None
+        try:
+            r = subprocess.run([sys.executable, "-c", _PROBE_SRC], capture_output=True, text=True, timeout=timeout_s)
+            if r.returncode == 0 and r.stdout.strip().startswith("{"):
+                result = json.loads(r.stdout.strip())
+        except Exception:
+            result = None
+        tmp = path + f".{os.getpid()}.tmp"
+        with open(tmp, "w") as f:
+            json.dump(result or {"closeness": None}, f)
+        os.replace(tmp, path)
+    else:
+        t0 = time.time()
+        while not os.path.exists(path) and time.time() - t0 < timeout_s + 30:
+            time.sleep(0.05)
+    try:
+        with open(path) as f:
+            c = json.load(f).get("closeness")
+    except Exception:
+        return None
+    if not c or len({c[i][j] for i in range(len(c)) for j in range(len(c)) if i != j}) <= 1:
+        return None
+    # two classes are enough: "shares an uplink" (clearly slowed down) or not
+    return [[1 if v >= 25 else 0 for v in row] for row in c]
+
+
 def spread_devices(count: int, closeness: Optional[List[List[int]]], n_visible: int) -> List[int]:
     """``count`` of the ``n_visible`` GPUs, chosen greedily so that the closest pair among them is as
     far apart on PCIe as possible (one GPU per switch before any switch gets a second one).
@@ -121,15 +201,20 @@ def spread_devices(count: int, closeness: Optional[List[List[int]]], n_visible: 
 
 def device_index_for(local_rank: int, local_world: Optional[int] = None) -> int:
     """GPU index for this rank.  When the job uses fewer GPUs than are visible (a 2- or 4-rank run on
-    an 8-GPU box) the ranks are spread over distinct PCIe uplinks instead of taking GPUs 0..N-1."""
+    an 8-GPU box) the ranks are spread over distinct PCIe uplinks instead of taking GPUs 0..N-1.  The
+    uplink sharing comes from NVML / sysfs, or - where the host hides its PCIe tree - from a one-off
+    measurement (``measured_pcie_closeness``; ``B200DP_PCIE_PROBE=0`` switches it off)."""
     import torch
 
     n = torch.cuda.device_count()
     if local_world is None:
         local_world = _first_int(os.environ, "LOCAL_WORLD_SIZE", "OMPI_COMM_WORLD_LOCAL_SIZE", "WORLD_SIZE") or 1
-    if os.environ.get("B200DP_PLACEMENT", "spread") != "spread" or local_world >= n or local_world < 1:
+    if os.environ.get("B200DP_PLACEMENT", "spread") != "spread" or local_world >= n or local_world <= 1:
         return local_rank % max(n, 1)
-    devs = spread_devices(local_world, pcie_closeness(), n)
+    closeness = pcie_closeness()
+    if closeness is None and os.environ.get("B200DP_PCIE_PROBE", "1") != "0":
+        closeness = measured_pcie_closeness()
+    devs = spread_devices(local_world, closeness, n)
     return devs[local_rank % len(devs)]
 
 

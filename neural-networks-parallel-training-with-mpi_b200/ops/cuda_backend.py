@@ -673,7 +673,8 @@ class CudaRuntime:
             self.sync: GradSync = CudaLocalSync(comm, weights, divisor, self.flat, self.buckets, overlap)
         elif fused:
             self.sync = FusedSync(comm, weights, divisor, sync_name, self.flat, self.symm, self.buckets,
-                                  overlap=overlap, max_blocks=0, timeout_ms=cfg.watchdog_ms)
+                                  overlap=overlap, max_blocks=int(__import__("os").environ.get("B200DP_SYNC_BLOCKS", "0")),
+                                  timeout_ms=cfg.watchdog_ms)
             self.device_broadcast = self._device_broadcast
             if calibrate and self.symm.buf.mc_ptr is not None:
                 sync_name = self.sync.calibrate(("fused_twoshot", "fused_nvls"))

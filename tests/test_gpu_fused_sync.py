@@ -168,3 +168,17 @@ def test_nvls_mode_refuses_unequal_weights():
                      mc_grads=bufs[0].data_ptr(), mc_params=bufs[0].data_ptr())
     with pytest.raises(B200dpError, match="equal per-rank weights"):
         ar.launch(a, 0, n, 0.1, 0.9, False)
+
+
+def test_sync_kernel_fits_beside_a_persistent_gemm_cta():
+    """The fused sync runs on a second stream while backward's GEMMs run, and its cross-GPU barrier
+    needs every one of its CTAs resident: one GEMM CTA + one sync CTA must fit an SM's 64 K registers.
+    (A GEMM epilogue that grew to 180 registers/thread once pushed the sync kernels out: they ran only
+    in the gaps between GEMMs and the 2-GPU step lost 0.2 ms.)"""
+    import ctypes as C
+    from b200dp.ops import _lib
+    lib = _lib.lib()
+    g, s = C.c_int(), C.c_int()
+    lib.b200dp_overlap_register_budget.argtypes = [C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    _lib.check(lib.b200dp_overlap_register_budget(C.byref(g), C.byref(s)))
+    assert 0 < g.value and 0 < s.value and g.value + s.value <= 65536, (g.value, s.value)

@@ -14,9 +14,16 @@ import bench  # noqa: E402
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--config", default="wide")
+    ap.add_argument("--gpus", type=int, default=1, help="under torchrun: world size (rank 0 prints its own timeline)")
+    ap.add_argument("--sync", default="auto")
+    ap.add_argument("--no-overlap", action="store_true")
     a = ap.parse_args()
-    args = argparse.Namespace(config=a.config, sync="auto", rows_per_gpu=None, no_overlap=False, bucket_mb=0.0)
-    t = bench.make_trainer(args, bench.CONFIGS[a.config], a.config, 1)
+    args = argparse.Namespace(config=a.config, sync=a.sync, rows_per_gpu=None, no_overlap=a.no_overlap, bucket_mb=0.0,
+                              gpus=a.gpus, impl="ours")
+    rank, world, _ = bench.dist_setup(args)
+    if rank != 0:
+        sys.stdout = open(os.devnull, "w")
+    t = bench.make_trainer(args, bench.CONFIGS[a.config], a.config, world)
     for _ in range(5):
         t.step(t.x, t.y)
     torch.cuda.synchronize()
@@ -49,6 +56,12 @@ def main():
     print("| kernel | total us over 3 steps |\n|---|---|")
     for k, v in sorted(busy.items(), key=lambda kv: -kv[1]):
         print(f"| {k} | {v:.1f} |")
+    sys.stdout.flush()
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+        t.close()
+        dist.destroy_process_group()
 
 
 if __name__ == "__main__":

@@ -48,7 +48,13 @@ def main():
                 row.append("  ?")
         print("  ", " ".join(row))
     c = pcie_closeness()
-    print("closeness matrix:", c)
+    print("closeness matrix (NVML / sysfs):", c)
+    if c is None and n > 2:
+        from b200dp.launch import measured_pcie_closeness
+        c = measured_pcie_closeness()
+        print("closeness matrix (measured: 1 = simultaneous H2D copies slow each other down):")
+        for row in c or []:
+            print("   ", row)
     for w in (2, 4):
         print(f"spread placement for {w} ranks:", spread_devices(w, c, n))
 
