@@ -316,8 +316,11 @@ sync_emulated_kernel(const SyncArgs* __restrict__ all) {
 
 template <typename G>
 const void* pick_kernel(int world, bool emulated) {
-  if (world <= 2) return emulated ? (const void*)sync_emulated_kernel<G, 2, 4> : (const void*)sync_kernel<G, 2, 4>;
-  if (world <= 4) return emulated ? (const void*)sync_emulated_kernel<G, 4, 3> : (const void*)sync_kernel<G, 4, 3>;
+  // U = 2 everywhere: 256 threads x 2 x (WR + 4) x 16 B = 48-96 KB of loads in flight per SM.  More looks
+  // better on an idle GPU (the sweep), but this kernel's job is to run beside backward's GEMMs, where
+  // the L1 that holds its in-flight lines is ~60 KB: measured at 2 GPUs, U = 4 was slower in the step.
+  if (world <= 2) return emulated ? (const void*)sync_emulated_kernel<G, 2, 2> : (const void*)sync_kernel<G, 2, 2>;
+  if (world <= 4) return emulated ? (const void*)sync_emulated_kernel<G, 4, 2> : (const void*)sync_kernel<G, 4, 2>;
   return emulated ? (const void*)sync_emulated_kernel<G, 8, 2> : (const void*)sync_kernel<G, 8, 2>;
 }
 

@@ -101,6 +101,7 @@ def pcie_closeness() -> Optional[List[List[int]]]:
 
 _PROBE_SRC = r"""
 import json, sys, torch
+count = int(sys.argv[1])
 n = torch.cuda.device_count()
 nbytes = 48 << 20
 host, dev, st = [], [], []
@@ -110,6 +111,7 @@ for i in range(n):
     dev.append(torch.empty(nbytes, dtype=torch.uint8, device=f"cuda:{i}"))
     st.append(torch.cuda.Stream(device=i))
 def run(ids, reps=3):
+    # every GPU in `ids` copies 2 x 48 MB from pinned host memory at the same time; worst GPU's best time
     best = {i: 1e9 for i in ids}
     for _ in range(reps):
         ev = {}
@@ -122,27 +124,31 @@ def run(ids, reps=3):
         for i in ids:
             torch.cuda.set_device(i); st[i].synchronize()
             best[i] = min(best[i], ev[i][0].elapsed_time(ev[i][1]))
-    return best
+    return max(best.values())
 for i in range(n):
     run([i], 1)
-alone = {i: run([i])[i] for i in range(n)}
-score = [[0] * n for _ in range(n)]
-for i in range(n):
-    for j in range(i + 1, n):
-        t = run([i, j])
-        slow = max(t[i] / alone[i], t[j] / alone[j])
-        score[i][j] = score[j][i] = int(round(100 * max(slow - 1.0, 0.0)))
-json.dump({"alone_ms": alone, "closeness": score}, sys.stdout)
+alone = [run([i]) for i in range(n)]
+chosen, log = [0], []
+while len(chosen) < min(count, n):
+    cands = [(run(chosen + [g]), g) for g in range(n) if g not in chosen]
+    t, g = min(cands)
+    log.append({"add": g, "ms": t, "all": [[round(a, 3), b] for a, b in cands]})
+    chosen.append(g)
+json.dump({"devices": chosen, "alone_ms": alone, "group_ms": run(chosen), "first_n_ms": run(list(range(min(count, n)))),
+           "log": log}, sys.stdout)
 """
 
 
-def measured_pcie_closeness(timeout_s: float = 90.0) -> Optional[List[List[int]]]:
-    """Where the PCIe topology is not visible (virtualised hosts give every GPU its own root complex and
-    NVML reports every pair as "same node"), find out by measurement which GPUs share a host uplink:
-    a pair whose simultaneous pinned H2D copies slow each other down shares one.  Entry = percent
-    slowdown of the pair's copies against each GPU copying alone.  Runs once per job, in a short-lived
-    child process of local rank 0 (so no rank keeps CUDA contexts on GPUs it does not use); the other
-    local ranks read the result from a file keyed by the launcher's pid."""
+def measured_spread(count: int, timeout_s: float = 120.0) -> Optional[List[int]]:
+    """Where the host hides its PCIe / NUMA layout (virtualised boxes give every GPU its own root complex,
+    NVML reports every pair as "same node", there is one NUMA node), pick the ``count`` GPUs by
+    measurement: start from GPU 0 and keep adding the GPU with which the group's simultaneous pinned
+    H2D copies finish soonest.  On this pool's 8-GPU boxes pairs never slow each other down, but four
+    GPUs of the same half of the box share ~115 GB/s of host bandwidth, so GPUs 0-3 feed at half rate
+    while two GPUs from each half feed at full rate.  Runs once per job, in a short-lived child process of
+    local rank 0 (no rank keeps CUDA contexts on GPUs it does not use); the other local ranks read the
+    result from a file keyed by the launcher's pid.  Returns None when the probe fails or finds nothing
+    better than GPUs 0..count-1."""
     import json
     import subprocess
     import sys
@@ -150,19 +156,20 @@ def measured_pcie_closeness(timeout_s: float = 90.0) -> Optional[List[List[int]]
     import time
 
     local_rank = _first_int(os.environ, "LOCAL_RANK", "OMPI_COMM_WORLD_LOCAL_RANK", "MPI_LOCALRANKID", "SLURM_LOCALID") or 0
-    key = f"b200dp_pcie_{os.getppid()}_{os.environ.get('MASTER_PORT', '0')}.json"
+    key = f"b200dp_pcie_{os.getppid()}_{os.environ.get('MASTER_PORT', '0')}_{count}.json"
     path = os.path.join(tempfile.gettempdir(), key)
     if local_rank == 0:
         result = None
         try:
-            r = subprocess.run([sys.executable, "-c", _PROBE_SRC], capture_output=True, text=True, timeout=timeout_s)
+            r = subprocess.run([sys.executable, "-c", _PROBE_SRC, str(count)], capture_output=True, text=True,
+                               timeout=timeout_s)
             if r.returncode == 0 and r.stdout.strip().startswith("{"):
                 result = json.loads(r.stdout.strip())
         except Exception:
             result = None
         tmp = path + f".{os.getpid()}.tmp"
         with open(tmp, "w") as f:
-            json.dump(result or {"closeness": None}, f)
+            json.dump(result or {"devices": None}, f)
         os.replace(tmp, path)
     else:
         t0 = time.time()
@@ -170,13 +177,15 @@ def measured_pcie_closeness(timeout_s: float = 90.0) -> Optional[List[List[int]]
             time.sleep(0.05)
     try:
         with open(path) as f:
-            c = json.load(f).get("closeness")
+            res = json.load(f)
     except Exception:
         return None
-    if not c or len({c[i][j] for i in range(len(c)) for j in range(len(c)) if i != j}) <= 1:
+    devs = res.get("devices")
+    if not devs or len(devs) != count or len(set(devs)) != count:
         return None
-    # two classes are enough: "shares an uplink" (clearly slowed down) or not
-    return [[1 if v >= 25 else 0 for v in row] for row in c]
+    if res.get("group_ms", 0) > 0.93 * res.get("first_n_ms", 0):      # nothing to gain: keep 0..count-1
+        return None
+    return [int(d) for d in devs]
 
 
 def spread_devices(count: int, closeness: Optional[List[List[int]]], n_visible: int) -> List[int]:
@@ -203,7 +212,7 @@ def device_index_for(local_rank: int, local_world: Optional[int] = None) -> int:
     """GPU index for this rank.  When the job uses fewer GPUs than are visible (a 2- or 4-rank run on
     an 8-GPU box) the ranks are spread over distinct PCIe uplinks instead of taking GPUs 0..N-1.  The
     uplink sharing comes from NVML / sysfs, or - where the host hides its PCIe tree - from a one-off
-    measurement (``measured_pcie_closeness``; ``B200DP_PCIE_PROBE=0`` switches it off)."""
+    measurement (``measured_spread``; ``B200DP_PCIE_PROBE=0`` switches it off)."""
     import torch
 
     n = torch.cuda.device_count()
@@ -212,9 +221,11 @@ def device_index_for(local_rank: int, local_world: Optional[int] = None) -> int:
     if os.environ.get("B200DP_PLACEMENT", "spread") != "spread" or local_world >= n or local_world <= 1:
         return local_rank % max(n, 1)
     closeness = pcie_closeness()
+    devs = None
     if closeness is None and os.environ.get("B200DP_PCIE_PROBE", "1") != "0":
-        closeness = measured_pcie_closeness()
-    devs = spread_devices(local_world, closeness, n)
+        devs = measured_spread(local_world)
+    if devs is None:
+        devs = spread_devices(local_world, closeness, n)
     return devs[local_rank % len(devs)]
 
 

@@ -50,11 +50,12 @@ def main():
     c = pcie_closeness()
     print("closeness matrix (NVML / sysfs):", c)
     if c is None and n > 2:
-        from b200dp.launch import measured_pcie_closeness
-        c = measured_pcie_closeness()
-        print("closeness matrix (measured: 1 = simultaneous H2D copies slow each other down):")
-        for row in c or []:
-            print("   ", row)
+        from b200dp.launch import measured_spread
+        for w in (2, 4):
+            print(f"measured placement for {w} ranks:", measured_spread(w))
+        import glob, json, tempfile
+        for f in sorted(glob.glob(os.path.join(tempfile.gettempdir(), "b200dp_pcie_*.json"))):
+            print(f, open(f).read()[:1500])
     for w in (2, 4):
         print(f"spread placement for {w} ranks:", spread_devices(w, c, n))
 
