@@ -244,31 +244,6 @@ def measure_ours(args, config_name, rank, world, sampler, extras=True):
     value = global_batch / (ms_per_step * 1e-3)
     final_loss = float(loss.item())
 
-    # ---- sustained: the same step for >= sustained_s seconds (power-capped steady state) --------
-    sustained = None
-    if extras and args.sustained_s > 0 and not config_name.startswith("ref"):
-        n = max(K, int(args.sustained_s * 1e3 / ms_per_step) + 1)
-        sms, _, sclk = timed.run(step, n)
-        sustained = {"steps": n, "seconds": sms / 1e3, "ms_per_step": sms / n,
-                     "value": global_batch / (sms / n * 1e-3), "clocks": clocks_field(sclk)}
-
-    # ---- grad-sync us/step: busy and exposed time of the fused sync + update kernels ------------
-    grad_sync = None
-    if extras and hasattr(t.sync, "start_profile") and not graphed:
-        t.sync.start_profile()
-        for _ in range(10):
-            step()
-        prof = t.sync.stop_profile()
-        if prof:
-            mine = {"busy_us": statistics.median(p["busy_us"] for p in prof),
-                    "exposed_us": statistics.median(p["exposed_us"] for p in prof),
-                    "kernels_per_step": prof[0]["kernels"]}
-            allr = gather_ranks(mine, world)
-            grad_sync = {"busy_us": max(a["busy_us"] for a in allr), "exposed_us": max(a["exposed_us"] for a in allr),
-                         "kernels_per_step": mine["kernels_per_step"],
-                         "how": "CUDA events around every sync(+update) kernel on the side stream (busy) and "
-                                "around the main stream's final join (exposed); median of 10 steps, max over ranks"}
-
     # ---- end to end: pinned host batches, H2D every step, loss read back every step -----------
     e2e = None
     if not args.no_e2e:
@@ -311,6 +286,32 @@ def measure_ours(args, config_name, rank, world, sampler, extras=True):
         del xh, yh
         for b in hb:
             b.close()
+
+    # ---- grad-sync us/step: busy and exposed time of the fused sync + update kernels ------------
+    grad_sync = None
+    if extras and hasattr(t.sync, "start_profile") and not graphed:
+        t.sync.start_profile()
+        for _ in range(10):
+            step()
+        prof = t.sync.stop_profile()
+        if prof:
+            mine = {"busy_us": statistics.median(p["busy_us"] for p in prof),
+                    "exposed_us": statistics.median(p["exposed_us"] for p in prof),
+                    "kernels_per_step": prof[0]["kernels"]}
+            allr = gather_ranks(mine, world)
+            grad_sync = {"busy_us": max(a["busy_us"] for a in allr), "exposed_us": max(a["exposed_us"] for a in allr),
+                         "kernels_per_step": mine["kernels_per_step"],
+                         "how": "CUDA events around every sync(+update) kernel on the side stream (busy) and "
+                                "around the main stream's final join (exposed); median of 10 steps, max over ranks"}
+
+    # ---- sustained: the same step for >= sustained_s seconds (power-capped steady state); last, so
+    # the end-to-end measurement above still sees the clocks the kernel-only one saw --------
+    sustained = None
+    if extras and args.sustained_s > 0 and not config_name.startswith("ref"):
+        n = max(K, int(args.sustained_s * 1e3 / ms_per_step) + 1)
+        sms, _, sclk = timed.run(step, n)
+        sustained = {"steps": n, "seconds": sms / 1e3, "ms_per_step": sms / n,
+                     "value": global_batch / (sms / n * 1e-3), "clocks": clocks_field(sclk)}
 
     spec = t.spec
     rec = {
