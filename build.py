@@ -23,6 +23,10 @@ FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-li
          "-I", os.path.join(ROOT, "include")]
 
 
+EXTRA = {}      # per-file nvcc flags (none at present)
+FLAGS += os.environ.get("B200DP_NVCC_EXTRA", "").split()      # A/B builds: -D switches (with --force)
+
+
 def sources():
     return sorted(glob.glob(os.path.join(ROOT, "csrc", "*.cu")))
 
@@ -46,7 +50,8 @@ def build(force=False, verbose=False):
 
     def compile_one(job):
         src, obj = job
-        r = subprocess.run([NVCC, *FLAGS, "-c", src, "-o", obj], capture_output=True, text=True)
+        r = subprocess.run([NVCC, *FLAGS, *EXTRA.get(os.path.basename(src), []), "-c", src, "-o", obj],
+                           capture_output=True, text=True)
         return src, r
 
     if jobs:

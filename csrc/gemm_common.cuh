@@ -1,8 +1,7 @@
 // Pieces shared by the single-CTA (gemm_tcgen05.cu) and CTA-pair (gemm_tcgen05_2cta.cu) Linear GEMMs:
 // element traits (bf16 -> kind::f16, fp32 -> kind::tf32), the persistent tile walk, UMMA shared-memory
 // and instruction descriptors, the epilogue (TMEM -> registers -> bias / ReLU / ReLU-mask -> global,
-// with the tcgen05.ld of the next 32 columns in flight while the current ones are converted and
-// stored, and the fused column sums that produce the bias gradient of the layer below), and the
+// and the fused column sums that produce the bias gradient of the layer below), and the
 // host-side tensor-map cache.
 #pragma once
 #include <string.h>
@@ -17,10 +16,9 @@ constexpr int kEpiThreads = 128;
 // Register budget of the GEMM kernels.  A persistent GEMM CTA (192 threads) must leave room on its SM
 // for one CTA of the fused gradient sync (256 threads x 128 registers = 32 K of the SM's 64 K
 // registers): the sync kernels run on a second stream WHILE backward's GEMMs run, and their cross-GPU
-// barrier needs all of their CTAs resident at once.  __launch_bounds__(192, 2) makes ptxas stay within
-// half of the register file (<= 168 registers/thread, 31.5 K per CTA); shared memory still limits the
-// GEMM itself to one CTA per SM.
-constexpr int kGemmMinCtas = 2;
+// barrier needs all of their CTAs resident at once.  The kernels compile to ~117 registers (23 K per
+// CTA); b200dp_overlap_register_budget + a test keep the sum within the register file.
+constexpr int kGemmMinCtas = 1;
 constexpr int kEpiBarrierId = 1;      // named barrier of the four epilogue warps
 
 // ---- element traits ---------------------------------------------------------------------------
@@ -298,17 +296,16 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t tadd
   float* cs_buf = cs_smem + parity * (4 * BN);     // [4][BN] of this tile (double-buffered by tile parity)
   float* cs_row = cs ? cs_buf + quad * BN : nullptr;
   constexpr int NC = BN / 32;
-  static_assert(NC % 2 == 0, "the epilogue ping-pongs two register sets");
-  uint32_t va[32], vb[32];
-  tmem_ld_32x32b_x32(taddr, va);
+  // One register set, load -> wait -> process.  (A two-set ping-pong that kept the next tcgen05.ld in
+  // flight was measured and dropped: it cost 50 more registers per thread, did nothing for a GEMM that
+  // runs alone - the epilogue hides under the next tile's main loop either way - and made the step with
+  // a co-running gradient sync 6 % slower.)
+  uint32_t va[32];
 #pragma unroll 1
-  for (int c = 0; c < NC; c += 2) {
+  for (int c = 0; c < NC; ++c) {
+    tmem_ld_32x32b_x32(taddr + c * 32, va);
     tmem_ld_wait();
-    tmem_ld_32x32b_x32(taddr + (c + 1) * 32, vb);            // in flight while `va` is processed
     epilogue_chunk<T>(p, va, row, row_ok, n0 + c * 32, lane, cs_row, c * 32);
-    tmem_ld_wait();
-    if (c + 2 < NC) tmem_ld_32x32b_x32(taddr + (c + 2) * 32, va);
-    epilogue_chunk<T>(p, vb, row, row_ok, n0 + (c + 1) * 32, lane, cs_row, (c + 1) * 32);
   }
   tc_fence_before();
   __syncwarp();
