@@ -88,3 +88,19 @@ def test_bench_counts_executed_flops():
     # forward + wgrad for every layer, dgrad for all but the first: 4.12 TFLOP, not the 4.95 of 6*N*D
     assert bench.executed_flops(sizes, rows) == 2.0 * rows * (3 * full - sizes[0] * sizes[1])
     assert abs(bench.executed_flops(sizes, rows) / 1e12 - 4.124) < 0.01
+
+
+def test_measured_placement_falls_back_without_gpus(monkeypatch, tmp_path):
+    """launch.measured_spread on a box where the probe cannot run (no GPU here): the child fails, the
+    answer file says so, and placement falls back to GPUs 0..N-1 instead of raising or hanging."""
+    import tempfile
+    from b200dp import launch
+    monkeypatch.setattr(tempfile, "tempdir", str(tmp_path))
+    monkeypatch.setenv("LOCAL_RANK", "0")
+    monkeypatch.setenv("MASTER_PORT", "45678")
+    import torch
+    if torch.cuda.is_available() and torch.cuda.device_count() > 2:
+        import pytest
+        pytest.skip("this test is about boxes where the probe fails")
+    assert launch.measured_spread(2, timeout_s=60.0) is None
+    assert launch.spread_devices(2, None, 8) == [0, 1]
