@@ -89,7 +89,7 @@ def dist_setup(args):
     local = int(os.environ.get("LOCAL_RANK", str(rank)))
     if world != args.gpus and world > 1:
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
-    if torch.cuda.is_available():
+    if torch.cuda.is_available() and args.impl != "reference":      # the reference arm is CPU-only: no GPU, none of our code
         import b200dp  # noqa: F401
         from b200dp.launch import bind_cpu_near_gpu, device_index_for
         dev = device_index_for(local, int(os.environ.get("LOCAL_WORLD_SIZE", str(world))))
