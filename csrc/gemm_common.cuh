@@ -37,7 +37,6 @@ template <> struct Elem<float> {
   static constexpr bool kTf32 = true;
   static constexpr CUtensorMapDataType kTma = CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
 };
-constexpr int kSwizzleElems(int bytes) { return 128 / bytes; }   // elements per 128-byte row
 
 struct GemmParams {
   int M, N, K;

@@ -52,7 +52,6 @@ class TinyCompute:
         self.scratch = K.scratch(K.tiny_mlp_scratch_bytes(flat.spec, max(max_rows, 1)), dev)
         self.loss = torch.zeros((), dtype=torch.float32, device=dev)
         self.bucket_hook: Optional[Callable[[int], None]] = None
-        self.aux_stream = None
 
     def prepare_batch(self, x, y):
         return x.to(torch.float32).contiguous(), y.to(torch.float32).contiguous()
@@ -116,7 +115,6 @@ class GemmCompute:
         self.gemm_cs_scratch = K.scratch(gemm.colsum_scratch_bytes(R, widest), dev)
         self.bucket_hook: Optional[Callable[..., None]] = None
         self.wgrad_chunks = {}            # layer -> [(row0, row1), ...] of its weight (set with the buckets)
-        self.aux_stream = None            # side stream of the sync strategy (unused by the compute path now)
         self.gemm_max_ctas = 0
         self.grad_scale = 1.0             # this rank's weight in the all-reduce, folded into dLoss/dYhat
         self._zero_targets = None
@@ -689,7 +687,6 @@ class CudaRuntime:
             if not tiny:
                 self.compute.wgrad_chunks = {l: [(b.row0, b.row1) for b in bs]
                                              for l, bs in self.sync.chunks_of.items()}
-            self.compute.aux_stream = self.sync.comm_stream
         self.sync_name = sync_name
 
     def _device_broadcast(self, params: torch.Tensor) -> None:
