@@ -196,3 +196,29 @@ def test_global_loss_is_the_sample_weighted_mean():
     res = run_threads(3, fn)
     want = sum(l * n for l, n, _ in res) / sum(n for _, n, _ in res)
     assert all(abs(g - want) < 1e-9 * abs(want) for _, _, g in res)
+
+
+def test_pinned_buffer_without_a_gpu_is_plain_host_memory():
+    import torch
+    from b200dp.data import PinnedBuffer, pinned_like
+    if torch.cuda.is_available():
+        import pytest
+        pytest.skip("CPU fallback only")
+    b = PinnedBuffer((4, 3), torch.float32)
+    assert b.tensor.shape == (4, 3) and b.tensor.dtype == torch.float32
+    c = pinned_like(torch.arange(6.0).reshape(2, 3))
+    assert c.tensor.tolist() == [[0.0, 1.0, 2.0], [3.0, 4.0, 5.0]]
+    b.close(); c.close()
+
+
+def test_clock_sampler_is_harmless_without_a_gpu():
+    import torch
+    from b200dp.utils.clocks import ClockSampler
+    if torch.cuda.is_available():
+        import pytest
+        pytest.skip("CPU fallback only")
+    s = ClockSampler(0, period_ms=5).start()
+    s.wait_first_sample(0.05)
+    s.mark()
+    out = s.stop()
+    assert out["samples"] == 0 and out["reasons"] == [] and out["sm_mhz"] is None
