@@ -156,7 +156,15 @@ def measured_spread(count: int, timeout_s: float = 120.0) -> Optional[List[int]]
     import time
 
     local_rank = _first_int(os.environ, "LOCAL_RANK", "OMPI_COMM_WORLD_LOCAL_RANK", "MPI_LOCALRANKID", "SLURM_LOCALID") or 0
-    key = f"b200dp_pcie_{os.getppid()}_{os.environ.get('MASTER_PORT', '0')}_{count}.json"
+    # the launcher process (torchrun agent / mpiexec / shell) is the same for every local rank; its pid plus
+    # its start time is unique per launch, so a stale file of an earlier job can never be picked up
+    ppid = os.getppid()
+    try:
+        with open(f"/proc/{ppid}/stat") as f:
+            born = f.read().rsplit(")", 1)[1].split()[19]
+    except Exception:
+        born = "0"
+    key = f"b200dp_pcie_{ppid}_{born}_{os.environ.get('MASTER_PORT', '0')}_{count}.json"
     path = os.path.join(tempfile.gettempdir(), key)
     if local_rank == 0:
         result = None
